@@ -1,0 +1,89 @@
+/* gpk.h -- C ABI of libgpk.so: exact-GP hot path (Gram, Cholesky, LML+gradient, predict) in FP64
+ * on sm_100a.  This is the drop-in boundary under the sklearn-style estimator
+ * (unmanned_aerial_vehicles_b200.GaussianProcessRegressor).  The reference has no FFI for this path: the
+ * interface replaced is the Python estimator used at /root/reference/src/px4/simple_gp.py:167-177,194 and
+ * src/px4/gp_trainer.py:163-179,197, whose arithmetic lives in scikit-learn 1.9.0
+ * (sklearn/gaussian_process/_gpr.py, kernels.py).  Each entry point cites the lines it replaces.
+ *
+ * Conventions
+ *   - every pointer named *_d is a DEVICE pointer to float64 (int for info/neg counters), row-major;
+ *     pointers named *_h are HOST pointers (tiny hyper-parameter vectors, copied by value into launches);
+ *   - `stream` is a cudaStream_t passed as void*; all calls are asynchronous on it, no allocation inside;
+ *   - factorisation buffers are NP x NP with NP = gpk_pad(N) (multiple of 128), leading dimension NP;
+ *   - return value: 0 ok; < 0 bad argument (-k = k-th argument) or -1000-cudaError; the LAPACK-style
+ *     "first non-PD leading minor" index is written to *info_d (device int, 0 = ok) so no call blocks.
+ */
+#ifndef GPK_H
+#define GPK_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPK_ABI_VERSION 1
+int gpk_abi_version(void);
+/* padded order of an N x N factorisation buffer (next multiple of 128, >= 128) */
+int gpk_pad(int N);
+/* number of doubles in the LML output vector: [lml, sum log diag L, y.alpha (T), g_c, g_ls (D), g_noise] */
+int gpk_lml_out_len(int D, int T);
+/* number of doubles of scratch gpk_lml_grad / gpk_lml_eval need */
+size_t gpk_grad_workspace_doubles(int N, int D);
+
+/* kernels.py:1530-1587 RBF.__call__(X) + :1374-1419 WhiteKernel + :1244-1296 ConstantKernel, and
+ * _gpr.py:589 K[diag] += alpha.  K_d (NP x NP): c*exp(-.5*|xi/l - xj/l|^2), diagonal (c+noise)+jitter,
+ * identity in the padding.  lower_only != 0 skips tiles strictly above the diagonal. */
+int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
+             double* K_d, int NP, int lower_only, void* stream);
+
+/* scipy.linalg.cholesky (dpotrf) at _gpr.py:352,591 fused with the triangular inverse.
+ * A_d in: lower triangle of K, out: lower factor L.  Mlow_d = L^-1 (lower), Mup_d = L^-T (upper). */
+int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream);
+
+/* cho_solve((L, True), y) at _gpr.py:363,601 via the explicit inverse: u = L^-1 y, alpha = L^-T u.
+ * y_d, u_d, alpha_d are (NP x T) with leading dimension T (rows >= N zero). */
+int gpk_potrs(const double* Mlow_d, const double* Mup_d, int NP, const double* y_d, double* u_d, double* alpha_d,
+              int T, void* stream);
+
+/* K^-1 = L^-T L^-1 (replaces cho_solve(L, eye(N)) at _gpr.py:631); lower tiles of Kinv_d are written. */
+int gpk_lauum(const double* Mup_d, double* Kinv_d, int NP, void* stream);
+
+/* _gpr.py:613-617 (lml) and :629-651 (gradient) without the (N,N,n_theta) tensor.
+ * out_d has gpk_lml_out_len(D,T) doubles; gradient entries are d lml / d log(param).
+ * Kinv_d may be NULL when with_grad == 0. */
+int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise,
+                 const double* L_d, const double* y_d, const double* alpha_d, int T, const double* Kinv_d, int NP,
+                 int with_grad, double* ws_d, double* out_d, void* stream);
+
+/* one whole log_marginal_likelihood(theta, eval_gradient) evaluation (_gpr.py:541-656):
+ * gram -> potrf_inv -> potrs -> [lauum -> gradient] -> finalize.  A_d, Mlow_d, Mup_d are NP x NP scratch
+ * (A_d ends as K^-1 lower tiles when with_grad, else as L).  y_d (NP x T, zero padded). */
+int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
+                 const double* y_d, int T, double* A_d, double* Mlow_d, double* Mup_d, double* u_d, double* alpha_d,
+                 int NP, int with_grad, double* ws_d, double* out_d, int* info_d, void* stream);
+
+/* kernels.py:1569-1570 (cdist branch): Ks_d (MP x NP) = c*rbf(Xq, Xtrain), zero in the padding. */
+int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, const double* inv_ls_h, double c,
+                   double* Ks_d, int MP, int NP, void* stream);
+
+/* _gpr.py:446-454: mean_d (Mq x T) = (Ks alpha) * y_std + y_mean */
+int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* alpha_d, int T, const double* y_mean_d,
+                     const double* y_std_d, double* mean_d, void* stream);
+
+/* _gpr.py:460-500: V = Ks L^-T, var = prior - rowsum(V^2) clamped at 0, std = sqrt(var * y_std^2).
+ * rowsq_d: scratch MP x (NP/128).  *neg_d is incremented per clamped row (the caller warns). */
+int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
+                    const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream);
+
+/* utilities */
+int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream);
+int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream);
+/* C (+)= alpha * A * B^T on the FP64 tensor pipe; M,N,K multiples of 128.  tri: 0 none, 1 lower, 2 upper */
+int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* C_d, int ldc, int M, int N, int K,
+                double alpha, int accumulate, int a_tri, int b_tri, int lower_only, void* stream);
+/* register-resident DMMA loop for the FP64 tensor peak; returns flops executed in *flops_h */
+int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,157 @@
+// gpk_api.cu -- extern "C" surface of libgpk.so (see include/gpk.h for the contract and citations).
+#include "gpk_common.cuh"
+#include "../../include/gpk.h"
+#include <string.h>
+
+// launchers defined in the other translation units
+int gpk_dp_of(int D);
+cudaError_t gpk_launch_gram(const double*, int, int, const GpkKernelParams&, double*, int, int, cudaStream_t);
+cudaError_t gpk_launch_cross_gram(const double*, int, const double*, int, int, const GpkKernelParams&, double*, int,
+                                  int, cudaStream_t);
+cudaError_t gpk_launch_lml_grad(const double*, int, int, const GpkKernelParams&, const double*, size_t, const double*,
+                                const double*, int, const double*, int, int, double*, double*, cudaStream_t);
+cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*, int, const double*, const double*,
+                                    double*, cudaStream_t);
+cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
+cudaError_t gpk_launch_extract_lower(const double*, int, double*, int, cudaStream_t);
+cudaError_t gpk_launch_pad_copy(const double*, int, int, double*, int, int, cudaStream_t);
+cudaError_t gpk_launch_copy_diag(const double*, int, int, double*, cudaStream_t);
+cudaError_t gpk_launch_potrf_inv(double*, int, double*, double*, int, int, int*, cudaStream_t);
+cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t);
+cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
+cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
+
+static int make_params(GpkKernelParams& p, int D, const double* inv_ls_h, double c, double noise, double jitter) {
+  if (D < 1 || D > GPK_MAXD) return -1;
+  memset(&p, 0, sizeof(p));
+  for (int d = 0; d < D; ++d) p.inv_ls[d] = inv_ls_h[d];
+  p.c = c; p.noise = noise; p.jitter = jitter; p.D = D;
+  return 0;
+}
+
+extern "C" {
+
+int gpk_abi_version(void) { return GPK_ABI_VERSION; }
+int gpk_pad(int N) { int n = ((N + GPK_TILE - 1) / GPK_TILE) * GPK_TILE; return n < GPK_TILE ? GPK_TILE : n; }
+int gpk_lml_out_len(int D, int T) { return 2 + T + 1 + D + 1; }
+size_t gpk_grad_workspace_doubles(int N, int D) {
+  size_t nt = (size_t)gpk_pad(N) / 64;
+  return nt * nt * (size_t)(gpk_dp_of(D) + 2) + (size_t)gpk_pad(N);
+}
+
+int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
+             double* K_d, int NP, int lower_only, void* stream) {
+  GpkKernelParams p;
+  if (!X_d) return -1; if (N < 1) return -2; if (make_params(p, D, inv_ls_h, c, noise, jitter)) return -3;
+  if (!K_d) return -8; if (NP != gpk_pad(N)) return -9;
+  GPK_CHECK(gpk_launch_gram(X_d, N, D, p, K_d, NP, lower_only, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream) {
+  if (!A_d) return -1; if (!Mlow_d) return -2; if (!Mup_d) return -3; if (NP < GPK_TILE || NP % GPK_TILE) return -4;
+  if (!info_d) return -5;
+  GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_potrs(const double* Mlow_d, const double* Mup_d, int NP, const double* y_d, double* u_d, double* alpha_d,
+              int T, void* stream) {
+  if (!Mlow_d) return -1; if (!Mup_d) return -2; if (NP % GPK_TILE) return -3; if (T < 1) return -7;
+  GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, (cudaStream_t)stream));
+  GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_lauum(const double* Mup_d, double* Kinv_d, int NP, void* stream) {
+  if (!Mup_d) return -1; if (!Kinv_d) return -2; if (NP % GPK_TILE) return -3;
+  GPK_CHECK(gpk_launch_lauum(Mup_d, NP, Kinv_d, NP, NP, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise,
+                 const double* L_d, const double* y_d, const double* alpha_d, int T, const double* Kinv_d, int NP,
+                 int with_grad, double* ws_d, double* out_d, void* stream) {
+  GpkKernelParams p;
+  if (make_params(p, D, inv_ls_h, c, noise, 0.0)) return -3;
+  if (T < 1) return -10;
+  if (with_grad && !Kinv_d) return -11;
+  GPK_CHECK(gpk_launch_lml_grad(X_d, N, D, p, L_d, (size_t)NP + 1, y_d, alpha_d, T, Kinv_d, NP, with_grad, ws_d, out_d,
+                                (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
+                 const double* y_d, int T, double* A_d, double* Mlow_d, double* Mup_d, double* u_d, double* alpha_d,
+                 int NP, int with_grad, double* ws_d, double* out_d, int* info_d, void* stream) {
+  GpkKernelParams p;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (make_params(p, D, inv_ls_h, c, noise, jitter)) return -3;
+  if (T < 1) return -9;
+  if (NP != gpk_pad(N)) return -15;
+  const size_t nt = (size_t)NP / 64;
+  double* diag = ws_d + nt * nt * (size_t)(gpk_dp_of(D) + 2);
+  GPK_CHECK(gpk_launch_gram(X_d, N, D, p, A_d, NP, 1, st));
+  GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st));
+  GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, st));
+  GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, st));
+  GPK_CHECK(gpk_launch_copy_diag(A_d, NP, NP, diag, st));
+  if (with_grad) GPK_CHECK(gpk_launch_lauum(Mup_d, NP, A_d, NP, NP, st));
+  p.jitter = 0.0;
+  GPK_CHECK(gpk_launch_lml_grad(X_d, N, D, p, diag, 1, y_d, alpha_d, T, A_d, NP, with_grad, ws_d, out_d, st));
+  return 0;
+}
+
+int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, const double* inv_ls_h, double c,
+                   double* Ks_d, int MP, int NP, void* stream) {
+  GpkKernelParams p;
+  if (Mq < 1) return -2; if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -5;
+  if (MP % GPK_TILE || MP < Mq) return -9; if (NP != gpk_pad(N)) return -10;
+  GPK_CHECK(gpk_launch_cross_gram(Xq_d, Mq, X_d, N, D, p, Ks_d, MP, NP, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* alpha_d, int T, const double* y_mean_d,
+                     const double* y_std_d, double* mean_d, void* stream) {
+  if (!Ks_d) return -1; if (T < 1) return -6;
+  GPK_CHECK(gpk_launch_predict_mean(Ks_d, Mq, N, NP, alpha_d, T, y_mean_d, y_std_d, mean_d, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
+                    const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream) {
+  if (MP % GPK_TILE || MP < Mq) return -3; if (NP % GPK_TILE) return -5;
+  GpkGemmArgs g{};
+  g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+  g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
+  GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
+  GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
+  return 0;
+}
+
+int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream) {
+  GPK_CHECK(gpk_launch_extract_lower(src_d, NP, dst_d, N, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream) {
+  if (RP < R) return -5; if (CP < C) return -6;
+  GPK_CHECK(gpk_launch_pad_copy(src_d, R, C, dst_d, RP, CP, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* C_d, int ldc, int M, int N, int K,
+                double alpha, int accumulate, int a_tri, int b_tri, int lower_only, void* stream) {
+  if ((M % GPK_TILE) || (N % GPK_TILE) || (K % GPK_TILE)) return -7;
+  GpkGemmArgs g{};
+  g.A = A_d; g.lda = lda; g.B = B_d; g.ldb = ldb; g.C = C_d; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.alpha = alpha;
+  g.accumulate = accumulate; g.a_tri = a_tri; g.b_tri = b_tri; g.lower_only = lower_only; g.epilogue = GPK_EPI_STORE;
+  GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream) {
+  GPK_CHECK(gpk_launch_dmma_probe(blocks, iters, sink_d, (cudaStream_t)stream));
+  // 256 threads = 8 warps, 16 independent m8n8k4 accumulators per warp, 512 flops each
+  if (flops_h) *flops_h = (double)blocks * 8.0 * 16.0 * 512.0 * (double)iters;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,182 @@
+// gpk_chol.cu -- recursive blocked FP64 Cholesky fused with the triangular inverse.
+//
+// Replaces scipy.linalg.cholesky (dpotrf; sklearn _gpr.py:352,591) and the N-right-hand-side
+// cho_solve(L, I) sklearn uses to form K^-1 (_gpr.py:631, 2N^3 flops) by
+//   potrf + trtri (2N^3/3) followed by lauum (N^3/3), all as large-K NT GEMMs on the FP64 tensor pipe.
+//
+// Buffers (NP x NP, NP % 128 == 0):
+//   A    : in  = lower triangle of K (+ identity padding), out = lower Cholesky factor L
+//   Mlow : out = L^-1 (lower; diagonal 128-blocks carry explicit zeros above the diagonal)
+//   Mup  : out = L^-T (upper; = Mlow transposed)
+// Recursion on [off, off+n):  n1 | n2 split at a multiple of 128
+//   rec(11);  L21 = A21 * M11^T;  A22 -= L21 L21^T;  rec(22);  M21 = -M22 * L21 * M11.
+#include "gpk_common.cuh"
+
+#define LEAF_LD 129
+#define LEAF_SMEM_BYTES ((GPK_TILE * LEAF_LD + GPK_TILE) * 8)
+
+// One CTA factors a 128x128 diagonal block in shared memory and inverts the factor.
+// info: first failing global pivot index + 1 (LAPACK convention), 0 if none (atomicMin on nonzero).
+__global__ void __launch_bounds__(256, 1)
+gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ Mlow, double* __restrict__ Mup,
+                          int ldm, int off, int* __restrict__ info) {
+  extern __shared__ double sm[];
+  double* T = sm;                          // [128][129]
+  double* dinv = sm + GPK_TILE * LEAF_LD;  // [128]
+  const int tid = threadIdx.x;
+  const int n = GPK_TILE;
+  double* Ab = A + (size_t)off * lda + off;
+  for (int idx = tid; idx < n * n; idx += 256) {
+    int r = idx >> 7, c = idx & 127;
+    T[r * LEAF_LD + c] = (c <= r) ? Ab[(size_t)r * lda + c] : 0.0;
+  }
+  __syncthreads();
+  // right-looking unblocked Cholesky; thread (tid & 127) owns a row, (tid >> 7) a column parity
+  const int row = tid & 127, par = tid >> 7;
+  for (int j = 0; j < n; ++j) {
+    double d = T[j * LEAF_LD + j];
+    if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
+      if (tid == 0) { int want = off + j + 1; int old = atomicCAS(info, 0, want); if (old != 0 && old > want) atomicMin(info, want); }
+      d = __longlong_as_double(0x7ff8000000000000LL);
+    }
+    d = sqrt(d);
+    __syncthreads();
+    if (par == 0) {
+      if (row == j) T[j * LEAF_LD + j] = d;
+      else if (row > j) T[row * LEAF_LD + j] /= d;
+    }
+    __syncthreads();
+    if (row > j) {
+      double lij = T[row * LEAF_LD + j];
+      for (int k = j + 1 + par; k <= row; k += 2) T[row * LEAF_LD + k] -= lij * T[k * LEAF_LD + j];
+    }
+    __syncthreads();
+  }
+  // write L (explicit zeros above the diagonal)
+  for (int idx = tid; idx < n * n; idx += 256) {
+    int r = idx >> 7, c = idx & 127;
+    Ab[(size_t)r * lda + c] = (c <= r) ? T[r * LEAF_LD + c] : 0.0;
+  }
+  if (tid < n) dinv[tid] = 1.0 / T[tid * LEAF_LD + tid];
+  __syncthreads();
+  // inverse: thread j solves L m_j = e_j; M[i][j] (i > j) is stored transposed in T's upper triangle
+  if (tid < n) {
+    const int j = tid;
+    for (int i = j + 1; i < n; ++i) {
+      double s = T[i * LEAF_LD + j] * dinv[j];
+      for (int k = j + 1; k < i; ++k) s += T[i * LEAF_LD + k] * T[j * LEAF_LD + k];
+      T[j * LEAF_LD + i] = -s * dinv[i];
+    }
+  }
+  __syncthreads();
+  double* Ml = Mlow + (size_t)off * ldm + off;
+  double* Mu = Mup + (size_t)off * ldm + off;
+  for (int idx = tid; idx < n * n; idx += 256) {
+    int r = idx >> 7, c = idx & 127;
+    double lo = (c < r) ? T[c * LEAF_LD + r] : (c == r ? dinv[r] : 0.0);  // M[r][c]
+    double up = (c > r) ? T[r * LEAF_LD + c] : (c == r ? dinv[r] : 0.0);  // M[c][r]
+    Ml[(size_t)r * ldm + c] = lo;
+    Mu[(size_t)r * ldm + c] = up;
+  }
+}
+
+struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err; };
+
+static void chol_rec(CholCtx& c, int off, int n) {
+  if (c.err != cudaSuccess) return;
+  if (n <= GPK_TILE) {
+    gpk_leaf_potrf_inv_kernel<<<1, 256, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info);
+    c.err = cudaGetLastError();
+    return;
+  }
+  const int n1 = GPK_TILE * ((n / GPK_TILE + 1) / 2), n2 = n - n1, o2 = off + n1;
+  chol_rec(c, off, n1);
+  if (c.err != cudaSuccess) return;
+  double* A21 = c.A + (size_t)o2 * c.lda + off;
+  double* Ml21 = c.Ml + (size_t)o2 * c.ldm + off;
+  double* Mu12 = c.Mu + (size_t)off * c.ldm + o2;
+  GpkGemmArgs g{};
+  // L21 = A21 * M11^T  (tmp in Mlow21, then copied over A21)
+  g.A = A21; g.lda = c.lda; g.B = c.Ml + (size_t)off * c.ldm + off; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
+  g.M = n2; g.N = n1; g.K = n1; g.alpha = 1.0; g.accumulate = 0; g.a_tri = GPK_TRI_NONE; g.b_tri = GPK_TRI_LOWER;
+  g.lower_only = 0; g.epilogue = GPK_EPI_STORE; g.rowsq = nullptr;
+  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  if ((c.err = gpk_launch_copy_block(Ml21, c.ldm, A21, c.lda, n2, n1, c.st)) != cudaSuccess) return;
+  // A22 -= L21 L21^T (lower tiles)
+  g = GpkGemmArgs{};
+  g.A = A21; g.lda = c.lda; g.B = A21; g.ldb = c.lda; g.C = c.A + (size_t)o2 * c.lda + o2; g.ldc = c.lda;
+  g.M = n2; g.N = n2; g.K = n1; g.alpha = -1.0; g.accumulate = 1; g.lower_only = 1; g.epilogue = GPK_EPI_STORE;
+  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  chol_rec(c, o2, n2);
+  if (c.err != cudaSuccess) return;
+  // Wt = Mt11 * L21^T  -> Mup12 (n1 x n2)
+  g = GpkGemmArgs{};
+  g.A = c.Mu + (size_t)off * c.ldm + off; g.lda = c.ldm; g.B = A21; g.ldb = c.lda; g.C = Mu12; g.ldc = c.ldm;
+  g.M = n1; g.N = n2; g.K = n1; g.alpha = 1.0; g.a_tri = GPK_TRI_UPPER; g.epilogue = GPK_EPI_STORE;
+  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  // M21 = -M22 * W  : C[m,j] = -sum_k M22[m,k] Wt[j,k]
+  g = GpkGemmArgs{};
+  g.A = c.Ml + (size_t)o2 * c.ldm + o2; g.lda = c.ldm; g.B = Mu12; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
+  g.M = n2; g.N = n1; g.K = n2; g.alpha = -1.0; g.a_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_STORE;
+  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  c.err = gpk_launch_transpose_block(Ml21, c.ldm, Mu12, c.ldm, n2, n1, c.st);
+}
+
+cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
+                                 cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gpk_leaf_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         LEAF_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  if (NP % GPK_TILE) return cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess};
+  chol_rec(c, 0, NP);
+  return c.err;
+}
+
+// K^-1 = L^-T L^-1 = Mup * Mup^T  (lower tiles of Kinv are written; diagonal tiles in full)
+cudaError_t gpk_launch_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, cudaStream_t st) {
+  GpkGemmArgs g{};
+  g.A = Mup; g.lda = ldm; g.B = Mup; g.ldb = ldm; g.C = Kinv; g.ldc = ldk; g.M = NP; g.N = NP; g.K = NP;
+  g.alpha = 1.0; g.accumulate = 0; g.a_tri = GPK_TRI_UPPER; g.b_tri = GPK_TRI_UPPER; g.lower_only = 1;
+  g.epilogue = GPK_EPI_STORE;
+  return gpk_launch_gemm_nt(g, st);
+}
+
+// out[i, t] = sum_k Mt[i, k] * v[k, t]  over k <= i (lower) or k >= i (upper); one warp per row.
+template <int TT>
+__global__ void gpk_trimv_kernel(const double* __restrict__ Mt, int ldm, int NP, const double* __restrict__ v,
+                                 int ldv, double* __restrict__ out, int ldo, int upper, int t0, int T) {
+  int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= NP) return;
+  int kb = upper ? row : 0, ke = upper ? NP : row + 1;
+  double acc[TT];
+#pragma unroll
+  for (int t = 0; t < TT; ++t) acc[t] = 0.0;
+  const double* mr = Mt + (size_t)row * ldm;
+  for (int k = kb + lane; k < ke; k += 32) {
+    double m = mr[k];
+#pragma unroll
+    for (int t = 0; t < TT; ++t)
+      if (t0 + t < T) acc[t] += m * v[(size_t)k * ldv + t0 + t];
+  }
+#pragma unroll
+  for (int t = 0; t < TT; ++t) {
+    double s = acc[t];
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0 && t0 + t < T) out[(size_t)row * ldo + t0 + t] = s;
+  }
+}
+cudaError_t gpk_launch_trimv(const double* Mt, int ldm, int NP, const double* v, int ldv, double* out, int ldo,
+                             int upper, int T, cudaStream_t st) {
+  int blocks = (NP * 32 + 255) / 256;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    gpk_trimv_kernel<4><<<blocks, 256, 0, st>>>(Mt, ldm, NP, v, ldv, out, ldo, upper, t0, T);
+  }
+  return cudaGetLastError();
+}

@@ -1,0 +1,323 @@
+// gpk_kernels.cu -- kernel-function kernels: Gram assembly, cross-Gram, LML-gradient contraction,
+// prediction finalisation.  Mirrors sklearn/gaussian_process/kernels.py:
+//   RBF.__call__ (:1530-1587), WhiteKernel.__call__/diag (:1374-1440), ConstantKernel (:1244-1296),
+//   Sum/Product (:838-990) for the algebra  c * RBF(iso|ARD) + WhiteKernel(noise).
+// Squared distances use the direct sum of squared differences of X/length_scale (what pdist/cdist
+// 'sqeuclidean' computes), not the |a|^2+|b|^2-2ab expansion, to keep 1e-13 parity near duplicates.
+#include "gpk_common.cuh"
+
+#define GRAD_TC 8  // targets per gradient pass
+#define KTILE 64   // 64x64 output tile, 256 threads, 4x4 micro-tile per thread
+
+template <int DP>
+__device__ __forceinline__ void load_scaled_rows(double (*s)[DP + 1], const double* __restrict__ X, int ldx, int r0,
+                                                 int nrows_valid, const GpkKernelParams& p, int tid) {
+  for (int idx = tid; idx < KTILE * DP; idx += 256) {
+    int r = idx / DP, d = idx % DP;
+    double v = 0.0;
+    if (r0 + r < nrows_valid && d < p.D) v = X[(size_t)(r0 + r) * ldx + d] * p.inv_ls[d];
+    s[r][d] = v;
+  }
+}
+
+// K[i,j] for the padded NP x NP buffer.  lower_only: only tiles with tj <= ti are produced.
+template <int DP>
+__global__ void __launch_bounds__(256) gpk_gram_kernel(const double* __restrict__ X, int ldx, int N, int NP,
+                                                       GpkKernelParams p, double* __restrict__ K, int ldk,
+                                                       int lower_only) {
+  const int tj = blockIdx.x, ti = blockIdx.y;
+  if (lower_only && (tj * KTILE) > (ti * KTILE + KTILE - 1)) return;
+  __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1];
+  const int tid = threadIdx.x, i0 = ti * KTILE, j0 = tj * KTILE;
+  load_scaled_rows<DP>(xi, X, ldx, i0, N, p, tid);
+  load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
+  __syncthreads();
+  const int ty = tid >> 4, tx = tid & 15;
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int li = ty * 4 + a, i = i0 + li;
+    double out[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int lj = tx * 4 + b, j = j0 + lj;
+      double d2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; d2 += df * df; }
+      double v;
+      if (i >= N || j >= N) v = (i == j) ? 1.0 : 0.0;
+      else if (i == j) v = (p.c + p.noise) + p.jitter;
+      else v = p.c * exp(-0.5 * d2);
+      out[b] = v;
+    }
+    double* dst = K + (size_t)i * ldk + j0 + tx * 4;
+    *reinterpret_cast<double2*>(dst) = make_double2(out[0], out[1]);
+    *reinterpret_cast<double2*>(dst + 2) = make_double2(out[2], out[3]);
+  }
+}
+
+// Kstar[q, j] = c * rbf(xq, xtrain_j)  (q < Mq, j < N), zero in the padding; MP x NP output.
+template <int DP>
+__global__ void __launch_bounds__(256) gpk_cross_gram_kernel(const double* __restrict__ Xq, int ldq, int Mq,
+                                                             const double* __restrict__ X, int ldx, int N,
+                                                             GpkKernelParams p, double* __restrict__ Ks, int ldk) {
+  __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1];
+  const int tid = threadIdx.x, i0 = blockIdx.y * KTILE, j0 = blockIdx.x * KTILE;
+  load_scaled_rows<DP>(xi, Xq, ldq, i0, Mq, p, tid);
+  load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
+  __syncthreads();
+  const int ty = tid >> 4, tx = tid & 15;
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int li = ty * 4 + a, i = i0 + li;
+    double out[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int lj = tx * 4 + b, j = j0 + lj;
+      double d2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; d2 += df * df; }
+      out[b] = (i < Mq && j < N) ? p.c * exp(-0.5 * d2) : 0.0;
+    }
+    double* dst = Ks + (size_t)i * ldk + j0 + tx * 4;
+    *reinterpret_cast<double2*>(dst) = make_double2(out[0], out[1]);
+    *reinterpret_cast<double2*>(dst + 2) = make_double2(out[2], out[3]);
+  }
+}
+
+// Gradient contraction (sklearn _gpr.py:629-651 without the (N,N,n_theta) tensor):
+//   W = sum_t alpha_t alpha_t^T - T * Kinv ;   acc[d]   = sum_ij W_ij Kc_ij (dx_d/l_d)^2   (d < D)
+//   acc[DP] = sum_ij W_ij Kc_ij  (d/dlog c),   acc[DP+1] = tr(W)  (d/dlog noise = 0.5*noise*tr W)
+// over the lower tiles (off-diagonal pairs counted twice).  partial[(block), DP+2].
+template <int DP>
+__global__ void __launch_bounds__(256) gpk_grad_kernel(const double* __restrict__ X, int ldx, int N,
+                                                       GpkKernelParams p, const double* __restrict__ alpha, int lda,
+                                                       int T, const double* __restrict__ Kinv, int ldk,
+                                                       double* __restrict__ partial, int accum) {
+  const int tj = blockIdx.x, ti = blockIdx.y;
+  const int bid = blockIdx.y * gridDim.x + blockIdx.x;
+  __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1];
+  __shared__ double ai[KTILE][GRAD_TC + 1], aj[KTILE][GRAD_TC + 1];
+  __shared__ double red[8][DP + 2];
+  const int tid = threadIdx.x, i0 = ti * KTILE, j0 = tj * KTILE;
+  double acc[DP + 2];
+#pragma unroll
+  for (int d = 0; d < DP + 2; ++d) acc[d] = 0.0;
+  if (tj <= ti) {
+    load_scaled_rows<DP>(xi, X, ldx, i0, N, p, tid);
+    load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
+    for (int idx = tid; idx < KTILE * T; idx += 256) {
+      int r = idx / T, t = idx % T;
+      ai[r][t] = (i0 + r < N) ? alpha[(size_t)(i0 + r) * lda + t] : 0.0;
+      aj[r][t] = (j0 + r < N) ? alpha[(size_t)(j0 + r) * lda + t] : 0.0;
+    }
+    __syncthreads();
+    const int ty = tid >> 4, tx = tid & 15;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const int li = ty * 4 + a, i = i0 + li;
+      const double* kr = Kinv + (size_t)i * ldk + j0 + tx * 4;
+      double2 k01 = *reinterpret_cast<const double2*>(kr), k23 = *reinterpret_cast<const double2*>(kr + 2);
+      double kin[4] = {k01.x, k01.y, k23.x, k23.y};
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int lj = tx * 4 + b, j = j0 + lj;
+        if (i >= N || j > i) continue;
+        double w = 0.0;
+        for (int t = 0; t < T; ++t) w += ai[li][t] * aj[lj][t];
+        w -= (double)T * kin[b];
+        if (i == j) { acc[DP] += w * p.c; acc[DP + 1] += w; continue; }
+        double sq[DP], d2 = 0.0;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; sq[d] = df * df; d2 += sq[d]; }
+        double we = 2.0 * w * p.c * exp(-0.5 * d2);
+#pragma unroll
+        for (int d = 0; d < DP; ++d) acc[d] += we * sq[d];
+        acc[DP] += we;
+      }
+    }
+  }
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int d = 0; d < DP + 2; ++d) {
+    double s = acc[d];
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) red[warp][d] = s;
+  }
+  __syncthreads();
+  if (tid < DP + 2) {
+    double s = 0.0;
+    for (int w = 0; w < 8; ++w) s += red[w][tid];
+    if (accum) s += partial[(size_t)bid * (DP + 2) + tid];
+    partial[(size_t)bid * (DP + 2) + tid] = s;
+  }
+}
+
+// Deterministic final reduction. out layout (doubles):
+//   [0] lml  [1] sum log diag L  [2..2+T) y_t.alpha_t   [2+T ..) g_c, g_ls[0..D), g_noise  (already * 0.5)
+__global__ void gpk_lml_finalize_kernel(const double* __restrict__ partial, int nblocks, int DPp2, int D, int N, int T,
+                                        const double* __restrict__ L, size_t lstep, const double* __restrict__ y, int ldy,
+                                        const double* __restrict__ alpha, int lda, GpkKernelParams p, int with_grad,
+                                        double* __restrict__ out) {
+  __shared__ double sh[256];
+  const int tid = threadIdx.x;
+  const int nq = 1 + T + (with_grad ? DPp2 : 0);
+  for (int q = 0; q < nq; ++q) {
+    double s = 0.0;
+    if (q == 0) { for (int i = tid; i < N; i += 256) s += log(L[(size_t)i * lstep]); }
+    else if (q <= T) { int t = q - 1; for (int i = tid; i < N; i += 256) s += y[(size_t)i * ldy + t] * alpha[(size_t)i * lda + t]; }
+    else { int d = q - 1 - T; for (int b = tid; b < nblocks; b += 256) s += partial[(size_t)b * DPp2 + d]; }
+    sh[tid] = s;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) { if (tid < o) sh[tid] += sh[tid + o]; __syncthreads(); }
+    if (tid == 0) {
+      double v = sh[0];
+      if (q == 0) out[1] = v;
+      else if (q <= T) out[2 + q - 1] = v;
+      else {
+        int d = q - 1 - T, DP = DPp2 - 2;
+        if (d < D) out[2 + T + 1 + d] = 0.5 * v;
+        else if (d == DP) out[2 + T] = 0.5 * v;
+        else if (d == DP + 1) out[2 + T + 1 + D] = 0.5 * p.noise * v;
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    double lml = 0.0;
+    for (int t = 0; t < T; ++t) lml += -0.5 * out[2 + t] - out[1] - 0.5 * (double)N * 1.8378770664093453;
+    out[0] = lml;
+  }
+}
+
+// mean[q,t] = (sum_j Ks[q,j] alpha[j,t]) * y_std[t] + y_mean[t]; one warp per query row.
+__global__ void gpk_predict_mean_kernel(const double* __restrict__ Ks, int ldk, int Mq, int N,
+                                        const double* __restrict__ alpha, int lda, int T,
+                                        const double* __restrict__ y_mean, const double* __restrict__ y_std,
+                                        double* __restrict__ mean, int ldm) {
+  int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= Mq) return;
+  const double* kr = Ks + (size_t)row * ldk;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    double acc[4] = {0, 0, 0, 0};
+    for (int j = lane; j < N; j += 32) {
+      double k = kr[j];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) if (t0 + t < T) acc[t] += k * alpha[(size_t)j * lda + t0 + t];
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      double s = acc[t];
+      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0 && t0 + t < T) mean[(size_t)row * ldm + t0 + t] = s * y_std[t0 + t] + y_mean[t0 + t];
+    }
+  }
+}
+
+// var = prior - sum_tiles rowsq ; negatives clamped to 0 and counted (sklearn _gpr.py:480-500)
+__global__ void gpk_predict_std_kernel(const double* __restrict__ rowsq, int ntiles, int Mq, double prior,
+                                       const double* __restrict__ y_std, int T, double* __restrict__ std_out,
+                                       int lds, int* __restrict__ neg_count) {
+  int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= Mq) return;
+  double s = 0.0;
+  for (int t = 0; t < ntiles; ++t) s += rowsq[(size_t)q * ntiles + t];
+  double var = prior - s;
+  if (var < 0.0) { atomicAdd(neg_count, 1); var = 0.0; }
+  for (int t = 0; t < T; ++t) std_out[(size_t)q * lds + t] = sqrt(var * (y_std[t] * y_std[t]));
+}
+
+// dst (N x N, ld N) = lower triangle of src's leading N x N block, zeros above (scipy's L_ layout)
+__global__ void gpk_extract_lower_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int N) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (c < N) dst[(size_t)r * N + c] = (c <= r) ? src[(size_t)r * lds + c] : 0.0;
+}
+
+// zero-pad copy: dst (RP x ldd) <- src (R x C), rest zero
+__global__ void gpk_pad_copy_kernel(const double* __restrict__ src, int lds, int R, int C, double* __restrict__ dst,
+                                    int ldd, int RP, int CP) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (c < CP && r < RP) dst[(size_t)r * ldd + c] = (r < R && c < C) ? src[(size_t)r * lds + c] : 0.0;
+}
+
+// ---- launchers -----------------------------------------------------------------------------
+#define DISPATCH_DP(D, CALL)                       \
+  do {                                             \
+    if ((D) <= 4) { CALL(4); }                     \
+    else if ((D) <= 8) { CALL(8); }                \
+    else if ((D) <= 12) { CALL(12); }              \
+    else if ((D) <= 16) { CALL(16); }              \
+    else { CALL(32); }                             \
+  } while (0)
+
+int gpk_dp_of(int D) { return D <= 4 ? 4 : D <= 8 ? 8 : D <= 12 ? 12 : D <= 16 ? 16 : 32; }
+
+cudaError_t gpk_launch_gram(const double* X, int N, int D, const GpkKernelParams& p, double* K, int NP,
+                            int lower_only, cudaStream_t st) {
+  dim3 grid(NP / KTILE, NP / KTILE);
+#define CALL(DPV) gpk_gram_kernel<DPV><<<grid, 256, 0, st>>>(X, D, N, NP, p, K, NP, lower_only)
+  DISPATCH_DP(D, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_cross_gram(const double* Xq, int Mq, const double* X, int N, int D, const GpkKernelParams& p,
+                                  double* Ks, int MP, int NP, cudaStream_t st) {
+  dim3 grid(NP / KTILE, MP / KTILE);
+#define CALL(DPV) gpk_cross_gram_kernel<DPV><<<grid, 256, 0, st>>>(Xq, D, Mq, X, D, N, p, Ks, NP)
+  DISPATCH_DP(D, CALL);
+#undef CALL
+  return cudaGetLastError();
+}
+
+// ws: (NP/64)^2 * (DP+2) doubles
+cudaError_t gpk_launch_lml_grad(const double* X, int N, int D, const GpkKernelParams& p, const double* L,
+                                size_t lstep, const double* y, const double* alpha, int T, const double* Kinv, int NP,
+                                int with_grad, double* ws, double* out, cudaStream_t st) {
+  const int DP = gpk_dp_of(D);
+  const int nt = NP / KTILE, nblocks = nt * nt;
+  if (with_grad) {
+    dim3 grid(nt, nt);
+    for (int t0 = 0; t0 < T; t0 += GRAD_TC) {
+      const int tc = (T - t0 < GRAD_TC) ? (T - t0) : GRAD_TC;
+#define CALL(DPV) gpk_grad_kernel<DPV><<<grid, 256, 0, st>>>(X, D, N, p, alpha + t0, T, tc, Kinv, NP, ws, t0 > 0)
+      DISPATCH_DP(D, CALL);
+#undef CALL
+    }
+  }
+  gpk_lml_finalize_kernel<<<1, 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out);
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_predict_mean(const double* Ks, int Mq, int N, int NP, const double* alpha, int T,
+                                    const double* y_mean, const double* y_std, double* mean, cudaStream_t st) {
+  int blocks = (int)(((size_t)Mq * 32 + 255) / 256);
+  gpk_predict_mean_kernel<<<blocks, 256, 0, st>>>(Ks, NP, Mq, N, alpha, T, T, y_mean, y_std, mean, T);
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_predict_std(const double* rowsq, int ntiles, int Mq, double prior, const double* y_std, int T,
+                                   double* std_out, int* neg, cudaStream_t st) {
+  gpk_predict_std_kernel<<<(Mq + 255) / 256, 256, 0, st>>>(rowsq, ntiles, Mq, prior, y_std, T, std_out, T, neg);
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_extract_lower(const double* src, int NP, double* dst, int N, cudaStream_t st) {
+  dim3 grid((N + 255) / 256, N);
+  gpk_extract_lower_kernel<<<grid, 256, 0, st>>>(src, NP, dst, N);
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_pad_copy(const double* src, int R, int C, double* dst, int RP, int CP, cudaStream_t st) {
+  dim3 grid((CP + 127) / 128, RP);
+  gpk_pad_copy_kernel<<<grid, 128, 0, st>>>(src, C, R, C, dst, CP, RP, CP);
+  return cudaGetLastError();
+}
+
+__global__ void gpk_copy_diag_kernel(const double* __restrict__ A, int lda, int n, double* __restrict__ d) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) d[i] = A[(size_t)i * lda + i];
+}
+cudaError_t gpk_launch_copy_diag(const double* A, int lda, int n, double* d, cudaStream_t st) {
+  gpk_copy_diag_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, d);
+  return cudaGetLastError();
+}
