@@ -1,0 +1,88 @@
+"""ctypes binding of libgpk.so (C ABI declared in include/gpk.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``csrc/Makefile``.  There is no CPU
+fallback: if the shared object is missing, every compute entry point raises ``GpkUnavailable``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgpk.so")
+
+# every symbol include/gpk.h declares (tests check the .so exports exactly these)
+SYMBOLS = (
+    "gpk_abi_version", "gpk_pad", "gpk_lml_out_len", "gpk_grad_workspace_doubles", "gpk_gram",
+    "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
+    "gpk_predict_mean", "gpk_predict_std", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
+    "gpk_dmma_probe",
+)
+
+
+class GpkUnavailable(RuntimeError):
+    pass
+
+
+class GpkError(RuntimeError):
+    pass
+
+
+_lib = None
+_p = C.c_void_p
+_i = C.c_int
+_d = C.c_double
+_dp = C.POINTER(C.c_double)
+
+
+def _declare(lib):
+    lib.gpk_abi_version.restype = _i
+    lib.gpk_pad.argtypes = [_i]
+    lib.gpk_lml_out_len.argtypes = [_i, _i]
+    lib.gpk_grad_workspace_doubles.argtypes = [_i, _i]
+    lib.gpk_grad_workspace_doubles.restype = C.c_size_t
+    lib.gpk_gram.argtypes = [_p, _i, _i, _dp, _d, _d, _d, _p, _i, _i, _p]
+    lib.gpk_potrf_inv.argtypes = [_p, _p, _p, _i, _p, _p]
+    lib.gpk_potrs.argtypes = [_p, _p, _i, _p, _p, _p, _i, _p]
+    lib.gpk_lauum.argtypes = [_p, _p, _i, _p]
+    lib.gpk_lml_grad.argtypes = [_p, _i, _i, _dp, _d, _d, _p, _p, _p, _i, _p, _i, _i, _p, _p, _p]
+    lib.gpk_lml_eval.argtypes = [_p, _i, _i, _dp, _d, _d, _d, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p]
+    lib.gpk_cross_gram.argtypes = [_p, _i, _p, _i, _i, _dp, _d, _p, _i, _i, _p]
+    lib.gpk_predict_mean.argtypes = [_p, _i, _i, _i, _p, _i, _p, _p, _p, _p]
+    lib.gpk_predict_std.argtypes = [_p, _i, _i, _p, _i, _d, _p, _i, _p, _p, _p, _p]
+    lib.gpk_extract_lower.argtypes = [_p, _i, _p, _i, _p]
+    lib.gpk_pad_copy.argtypes = [_p, _i, _i, _p, _i, _i, _p]
+    lib.gpk_gemm_nt.argtypes = [_p, _i, _p, _i, _p, _i, _i, _i, _i, _d, _i, _i, _i, _i, _p]
+    lib.gpk_dmma_probe.argtypes = [_i, _i, _p, _dp, _p]
+    for name in SYMBOLS:
+        fn = getattr(lib, name)
+        if name not in ("gpk_grad_workspace_doubles",):
+            fn.restype = _i
+
+
+def load():
+    """Load libgpk.so (once).  Raises GpkUnavailable if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GpkUnavailable(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "or `make -C unmanned_aerial_vehicles_b200/csrc`. There is no CPU fallback."
+            )
+        lib = C.CDLL(LIB_PATH)
+        _declare(lib)
+        if lib.gpk_abi_version() != 1:
+            raise GpkUnavailable("libgpk.so ABI version mismatch; rebuild")
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        raise GpkError(f"{what} failed with code {rc}" + (" (CUDA error %d)" % (-rc - 1000) if rc <= -1000 else ""))
+
+
+def darr(values):
+    """host double array for the *_h arguments"""
+    vals = [float(v) for v in values]
+    return (C.c_double * len(vals))(*vals)

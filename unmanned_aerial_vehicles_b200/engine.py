@@ -1,0 +1,196 @@
+"""Device-side state of one exact GP (one kernel shared by T targets) on one B200.
+
+Host code is plumbing only: torch allocates HBM and supplies the stream; every flop runs in libgpk.so
+through the C ABI (include/gpk.h).  Mirrors the arithmetic of sklearn/gaussian_process/_gpr.py
+(:349-367 final factorisation, :541-656 LML + gradient, :446-500 predict).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+
+def _torch_cuda():
+    import torch
+
+    if not torch.cuda.is_available():
+        raise _lib.GpkUnavailable("no CUDA device: the GP hot path has no CPU fallback")
+    return torch
+
+
+class DeviceGP:
+    """Training set resident in HBM plus the three NP x NP factorisation buffers."""
+
+    def __init__(self, X: np.ndarray, y2d: np.ndarray, jitter: float, device=None):
+        torch = _torch_cuda()
+        self.torch = torch
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        y2d = np.ascontiguousarray(y2d, dtype=np.float64)
+        self.N, self.D = X.shape
+        self.T = y2d.shape[1]
+        if self.D > 32:
+            raise ValueError("libgpk supports at most 32 features")
+        self.NP = int(self.lib.gpk_pad(self.N))
+        self.jitter = float(jitter)
+        with torch.cuda.device(self.device):
+            # inputs come from pinned host memory so the copies can overlap the first launch
+            self.X_d = torch.from_numpy(X).pin_memory().to(self.device, non_blocking=True)
+            self.y_d = torch.zeros((self.NP, self.T), dtype=torch.float64, device=self.device)
+            self.y_d[: self.N].copy_(torch.from_numpy(y2d).pin_memory(), non_blocking=True)
+            self.u_d = torch.zeros((self.NP, self.T), dtype=torch.float64, device=self.device)
+            self.alpha_d = torch.zeros((self.NP, self.T), dtype=torch.float64, device=self.device)
+            nws = int(self.lib.gpk_grad_workspace_doubles(self.N, self.D))
+            self.ws_d = torch.empty(nws, dtype=torch.float64, device=self.device)
+            self.out_len = int(self.lib.gpk_lml_out_len(self.D, self.T))
+            self.out_d = torch.zeros(self.out_len, dtype=torch.float64, device=self.device)
+            self.out_h = torch.zeros(self.out_len + 1, dtype=torch.float64).pin_memory()
+            self.info_d = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.A_d = self.Mlow_d = self.Mup_d = None
+        self.factored = None  # (inv_ls tuple, c, noise) of the factor currently held in Mlow/alpha
+        self.a_holds_L = False
+        self.launches = 0
+
+    # -- helpers ---------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _bufs(self):
+        if self.A_d is None:
+            t = self.torch
+            shape = (self.NP, self.NP)
+            self.A_d = t.empty(shape, dtype=t.float64, device=self.device)
+            self.Mlow_d = t.empty(shape, dtype=t.float64, device=self.device)
+            self.Mup_d = t.empty(shape, dtype=t.float64, device=self.device)
+
+    @staticmethod
+    def _p(t):
+        return C.c_void_p(t.data_ptr())
+
+    # -- log marginal likelihood (+ gradient) ------------------------------------------------
+    def lml(self, inv_ls, c: float, noise: float, with_grad: bool):
+        """Returns (lml, g_c, g_ls[D], g_noise); lml = -inf when K is not positive definite
+        (sklearn _gpr.py:592-593).  Gradients are w.r.t. log-parameters."""
+        t = self.torch
+        self._bufs()
+        with t.cuda.device(self.device):
+            rc = self.lib.gpk_lml_eval(
+                self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter, self._p(self.y_d), self.T,
+                self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self._p(self.u_d), self._p(self.alpha_d),
+                self.NP, int(bool(with_grad)), self._p(self.ws_d), self._p(self.out_d), self._p(self.info_d),
+                self._stream())
+            _lib.check(rc, "gpk_lml_eval")
+            # one device->host read per evaluation: [out..., info]
+            self.out_h[: self.out_len].copy_(self.out_d, non_blocking=True)
+            info = self.info_d[:1].to("cpu", non_blocking=False)
+        self.factored = None
+        self.a_holds_L = False
+        out = self.out_h[: self.out_len].numpy().copy()
+        T, D = self.T, self.D
+        if int(info[0]) != 0 or not np.isfinite(out[0]):
+            return -np.inf, 0.0, np.zeros(D), 0.0
+        return float(out[0]), float(out[2 + T]), out[3 + T: 3 + T + D].copy(), float(out[3 + T + D])
+
+    # -- final factorisation ---------------------------------------------------------------
+    def factor(self, inv_ls, c: float, noise: float):
+        """gram -> potrf+inverse -> potrs.  Returns LAPACK-style info (0 ok)."""
+        t = self.torch
+        self._bufs()
+        key = (tuple(float(v) for v in inv_ls), float(c), float(noise))
+        with t.cuda.device(self.device):
+            st = self._stream()
+            _lib.check(self.lib.gpk_gram(self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter,
+                                         self._p(self.A_d), self.NP, 1, st), "gpk_gram")
+            _lib.check(self.lib.gpk_potrf_inv(self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self.NP,
+                                              self._p(self.info_d), st), "gpk_potrf_inv")
+            _lib.check(self.lib.gpk_potrs(self._p(self.Mlow_d), self._p(self.Mup_d), self.NP, self._p(self.y_d),
+                                          self._p(self.u_d), self._p(self.alpha_d), self.T, st), "gpk_potrs")
+            info = int(self.info_d[:1].cpu()[0])
+        self.factored = key if info == 0 else None
+        self.a_holds_L = info == 0
+        return info
+
+    def L_host(self) -> np.ndarray:
+        assert self.a_holds_L
+        t = self.torch
+        with t.cuda.device(self.device):
+            dst = t.empty((self.N, self.N), dtype=t.float64, device=self.device)
+            _lib.check(self.lib.gpk_extract_lower(self._p(self.A_d), self.NP, self._p(dst), self.N, self._stream()),
+                       "gpk_extract_lower")
+            return dst.cpu().numpy()
+
+    def alpha_host(self) -> np.ndarray:
+        return self.alpha_d[: self.N].cpu().numpy()
+
+    def gram_host(self, inv_ls, c, noise, jitter=0.0) -> np.ndarray:
+        """Full K (for parity tests of the Gram kernel)."""
+        t = self.torch
+        with t.cuda.device(self.device):
+            K = t.empty((self.NP, self.NP), dtype=t.float64, device=self.device)
+            _lib.check(self.lib.gpk_gram(self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, jitter,
+                                         self._p(K), self.NP, 0, self._stream()), "gpk_gram")
+            return K[: self.N, : self.N].cpu().numpy()
+
+    # -- predict -------------------------------------------------------------------------------
+    def predict(self, Xq: np.ndarray, y_mean, y_std, return_std: bool, return_cov: bool = False, chunk_rows=None):
+        """mean (M,T) [, std (M,T) | cov (M,M) un-normalised] for the factor currently held."""
+        assert self.factored is not None, "factor() first"
+        t = self.torch
+        inv_ls, c, noise = self.factored
+        Xq = np.ascontiguousarray(Xq, dtype=np.float64)
+        M = Xq.shape[0]
+        NP, T = self.NP, self.T
+        if chunk_rows is None:
+            chunk_rows = int(min(16384, max(128, (2 << 30) // (NP * 8))))
+        chunk_rows = max(128, (chunk_rows // 128) * 128)
+        if return_cov:
+            chunk_rows = ((M + 127) // 128) * 128
+        mean = np.empty((M, T))
+        std = np.empty((M, T)) if return_std else None
+        cov = None
+        neg_total = 0
+        with t.cuda.device(self.device):
+            st = self._stream()
+            ym = t.as_tensor(np.broadcast_to(np.asarray(y_mean, dtype=np.float64), (T,)).copy(), device=self.device)
+            ys = t.as_tensor(np.broadcast_to(np.asarray(y_std, dtype=np.float64), (T,)).copy(), device=self.device)
+            MPmax = min(chunk_rows, ((M + 127) // 128) * 128)
+            Ks = t.empty((MPmax, NP), dtype=t.float64, device=self.device)
+            mean_d = t.empty((MPmax, T), dtype=t.float64, device=self.device)
+            if return_std:
+                rowsq = t.empty((MPmax, NP // 128), dtype=t.float64, device=self.device)
+                std_d = t.empty((MPmax, T), dtype=t.float64, device=self.device)
+                neg_d = t.zeros(1, dtype=t.int32, device=self.device)
+            inv_h = _lib.darr(inv_ls)
+            Xq_pin = t.from_numpy(Xq).pin_memory()
+            for s in range(0, M, chunk_rows):
+                m = min(chunk_rows, M - s)
+                MP = ((m + 127) // 128) * 128
+                xq_d = Xq_pin[s:s + m].to(self.device, non_blocking=True)
+                _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(self.X_d), self.N, self.D, inv_h, c,
+                                                   self._p(Ks), MP, NP, st), "gpk_cross_gram")
+                _lib.check(self.lib.gpk_predict_mean(self._p(Ks), m, self.N, NP, self._p(self.alpha_d), T, self._p(ym),
+                                                     self._p(ys), self._p(mean_d), st), "gpk_predict_mean")
+                if return_std:
+                    _lib.check(self.lib.gpk_predict_std(self._p(Ks), m, MP, self._p(self.Mlow_d), NP, c + noise,
+                                                        self._p(ys), T, self._p(rowsq), self._p(std_d), self._p(neg_d),
+                                                        st), "gpk_predict_std")
+                    std[s:s + m] = std_d[:m].cpu().numpy()
+                if return_cov:
+                    V = t.empty((MP, NP), dtype=t.float64, device=self.device)
+                    _lib.check(self.lib.gpk_gemm_nt(self._p(Ks), NP, self._p(self.Mlow_d), NP, self._p(V), NP, MP, NP,
+                                                    NP, 1.0, 0, 0, 1, 0, st), "gpk_gemm_nt")
+                    Kqq = t.empty((MP, MP), dtype=t.float64, device=self.device)
+                    _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(xq_d), m, self.D, inv_h, c,
+                                                       self._p(Kqq), MP, MP, st), "gpk_cross_gram")
+                    _lib.check(self.lib.gpk_gemm_nt(self._p(V), NP, self._p(V), NP, self._p(Kqq), MP, MP, MP, NP,
+                                                    -1.0, 1, 0, 0, 0, st), "gpk_gemm_nt")
+                    cov = Kqq[:m, :m].cpu().numpy()
+                    cov[np.diag_indices_from(cov)] += noise
+                mean[s:s + m] = mean_d[:m].cpu().numpy()
+            if return_std:
+                neg_total = int(neg_d.cpu()[0])
+        return mean, std, cov, neg_total

@@ -1,0 +1,259 @@
+"""``GaussianProcessRegressor`` with scikit-learn's surface, computed on a B200 through libgpk.so.
+
+Drop-in for the estimator the reference constructs at src/px4/simple_gp.py:170-175 and
+src/px4/gp_trainer.py:169-174 and pickles under ``['gp_model']`` (src/px4/train_gp_offline.py:188-197).
+Behaviour follows sklearn 1.9.0 ``sklearn/gaussian_process/_gpr.py``: fit :233-368, predict :370-500,
+sample_y :502-539, log_marginal_likelihood :541-656, _constrained_optimization :658-674.  The L-BFGS-B
+driver stays SciPy on the host (n_theta <= 34); each objective evaluation is one ``gpk_lml_eval`` call.
+"""
+from __future__ import annotations
+
+import warnings
+from operator import itemgetter
+
+import numpy as np
+import scipy.optimize
+from sklearn.base import BaseEstimator, MultiOutputMixin, RegressorMixin, clone
+from sklearn.gaussian_process.kernels import RBF
+from sklearn.gaussian_process.kernels import ConstantKernel as C
+from sklearn.preprocessing._data import _handle_zeros_in_scale
+from sklearn.utils import check_random_state
+from sklearn.utils.optimize import _check_optimize_result
+from sklearn.utils.validation import check_array, check_X_y
+
+from .engine import DeviceGP
+from .kernel_lowering import assemble_gradient, lower
+
+
+class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
+    """Exact GP regression, FP64, on one B200 (no CPU fallback).
+
+    Same constructor as sklearn (_gpr.py:211-230).  ``alpha`` must be a scalar; kernels are limited to
+    ``[ConstantKernel*]RBF[+WhiteKernel]`` (see kernel_lowering.py).
+    """
+
+    def __init__(self, kernel=None, *, alpha=1e-10, optimizer="fmin_l_bfgs_b", n_restarts_optimizer=0,
+                 normalize_y=False, copy_X_train=True, n_targets=None, random_state=None):
+        self.kernel = kernel
+        self.alpha = alpha
+        self.optimizer = optimizer
+        self.n_restarts_optimizer = n_restarts_optimizer
+        self.normalize_y = normalize_y
+        self.copy_X_train = copy_X_train
+        self.n_targets = n_targets
+        self.random_state = random_state
+
+    # ------------------------------------------------------------------------------------------
+    def _scalar_alpha(self):
+        a = self.alpha
+        if np.iterable(a):
+            a = np.asarray(a)
+            if a.shape[0] == 1:
+                return float(a[0])
+            raise NotImplementedError("per-sample alpha arrays are not supported by the B200 path")
+        return float(a)
+
+    def _engine_for_training(self):
+        eng = getattr(self, "_engine", None)
+        if eng is None:
+            y2d = self.y_train_ if self.y_train_.ndim == 2 else self.y_train_[:, None]
+            eng = DeviceGP(self.X_train_, y2d, self._scalar_alpha())
+            self._engine = eng
+        return eng
+
+    def fit(self, X, y):
+        self.kernel_ = C(1.0, constant_value_bounds="fixed") * RBF(1.0, length_scale_bounds="fixed") \
+            if self.kernel is None else clone(self.kernel)
+        self._rng = check_random_state(self.random_state)
+        X, y = check_X_y(X, y, multi_output=True, y_numeric=True, ensure_2d=True, dtype="numeric")
+        X = np.asarray(X, dtype=np.float64)
+        y = np.asarray(y, dtype=np.float64)
+        self.n_features_in_ = X.shape[1]
+        n_targets_seen = y.shape[1] if y.ndim > 1 else 1
+        if self.n_targets is not None and n_targets_seen != self.n_targets:
+            raise ValueError("The number of targets seen in `y` is different from the parameter "
+                             f"`n_targets`. Got {n_targets_seen} != {self.n_targets}.")
+        if self.normalize_y:
+            self._y_train_mean = np.mean(y, axis=0)
+            self._y_train_std = _handle_zeros_in_scale(np.std(y, axis=0), copy=False)
+            y = (y - self._y_train_mean) / self._y_train_std
+        else:
+            shape_y_stats = (y.shape[1],) if y.ndim == 2 else 1
+            self._y_train_mean = np.zeros(shape=shape_y_stats)
+            self._y_train_std = np.ones(shape=shape_y_stats)
+        self._scalar_alpha()
+        self.X_train_ = np.copy(X) if self.copy_X_train else X
+        self.y_train_ = np.copy(y) if self.copy_X_train else y
+        self._engine = None
+        self._low = None
+        lower(self.kernel_, X.shape[1])  # raises early for unsupported kernels
+
+        if self.optimizer is not None and self.kernel_.n_dims > 0:
+            def obj_func(theta, eval_gradient=True):
+                if eval_gradient:
+                    lml, grad = self.log_marginal_likelihood(theta, eval_gradient=True, clone_kernel=False)
+                    return -lml, -grad
+                return -self.log_marginal_likelihood(theta, clone_kernel=False)
+
+            optima = [self._constrained_optimization(obj_func, self.kernel_.theta, self.kernel_.bounds)]
+            if self.n_restarts_optimizer > 0:
+                if not np.isfinite(self.kernel_.bounds).all():
+                    raise ValueError("Multiple optimizer restarts (n_restarts_optimizer>0) "
+                                     "requires that all bounds are finite.")
+                bounds = self.kernel_.bounds
+                for _ in range(self.n_restarts_optimizer):
+                    theta_initial = self._rng.uniform(bounds[:, 0], bounds[:, 1])
+                    optima.append(self._constrained_optimization(obj_func, theta_initial, bounds))
+            lml_values = list(map(itemgetter(1), optima))
+            self.kernel_.theta = optima[np.argmin(lml_values)][0]
+            self.kernel_._check_bounds_params()
+            self.log_marginal_likelihood_value_ = -np.min(lml_values)
+        else:
+            self.log_marginal_likelihood_value_ = self.log_marginal_likelihood(self.kernel_.theta, clone_kernel=False)
+        self._finalize_factor()
+        return self
+
+    def _finalize_factor(self):
+        """K + alpha I = L L^T, alpha_ = K^-1 y for kernel_ (_gpr.py:349-367)."""
+        eng = self._engine_for_training()
+        low = lower(self.kernel_, self.X_train_.shape[1])
+        info = eng.factor(1.0 / low.length_scale, low.c, low.noise)
+        if info != 0:
+            raise np.linalg.LinAlgError(
+                f"The kernel, {self.kernel_}, is not returning a positive definite matrix. Try gradually "
+                "increasing the 'alpha' parameter of your GaussianProcessRegressor estimator.",
+                f"{info}-th leading minor of the array is not positive definite")
+        self._low = low
+        a = eng.alpha_host()
+        self.alpha_ = a if self.y_train_.ndim == 2 else a[:, 0]
+        self.__dict__.pop("_L_cache", None)
+
+    @property
+    def L_(self):
+        """Lower Cholesky factor (downloaded on first access; upper triangle zero like SciPy's)."""
+        if "_L_cache" not in self.__dict__:
+            if not hasattr(self, "X_train_"):
+                raise AttributeError("L_")
+            self._ensure_factored(need_L=True)
+            self.__dict__["_L_cache"] = self._engine.L_host()
+        return self.__dict__["_L_cache"]
+
+    def _ensure_factored(self, need_L=False):
+        eng = getattr(self, "_engine", None)
+        if eng is None or eng.factored is None or self._low is None or (need_L and not eng.a_holds_L):
+            self._finalize_factor()
+
+    # ------------------------------------------------------------------------------------------
+    def predict(self, X, return_std=False, return_cov=False):
+        if return_std and return_cov:
+            raise RuntimeError("At most one of return_std or return_cov can be requested.")
+        X = check_array(X, ensure_2d=True, dtype="numeric")
+        if not hasattr(self, "X_train_"):  # prior (_gpr.py:417-443)
+            kernel = C(1.0, constant_value_bounds="fixed") * RBF(1.0, length_scale_bounds="fixed") \
+                if self.kernel is None else self.kernel
+            n_targets = self.n_targets if self.n_targets is not None else 1
+            y_mean = np.zeros(shape=(X.shape[0], n_targets)).squeeze()
+            low = lower(kernel, X.shape[1])
+            if return_cov:
+                raise NotImplementedError("prior covariance is not on the B200 path; fit first")
+            if return_std:
+                y_var = np.full(X.shape[0], low.c + low.noise)
+                if n_targets > 1:
+                    y_var = np.repeat(np.expand_dims(y_var, -1), repeats=n_targets, axis=-1)
+                return y_mean, np.sqrt(y_var)
+            return y_mean
+        if X.shape[1] != self.X_train_.shape[1]:
+            raise ValueError(f"X has {X.shape[1]} features, but GaussianProcessRegressor is expecting "
+                             f"{self.X_train_.shape[1]} features as input.")
+        self._ensure_factored()
+        eng = self._engine
+        T = eng.T
+        mean, std, cov, nneg = eng.predict(X, np.broadcast_to(self._y_train_mean, (T,)),
+                                           np.broadcast_to(self._y_train_std, (T,)), return_std, return_cov)
+        y_mean = mean
+        if self.y_train_.ndim == 1 or T == 1:
+            y_mean = mean[:, 0]
+        if return_cov:
+            y_cov = np.outer(cov, np.broadcast_to(self._y_train_std, (T,)) ** 2).reshape(*cov.shape, -1)
+            if y_cov.shape[2] == 1:
+                y_cov = np.squeeze(y_cov, axis=2)
+            return y_mean, y_cov
+        if return_std:
+            if nneg:
+                warnings.warn("Predicted variances smaller than 0. Setting those variances to 0.")
+            y_std = std[:, 0] if std.shape[1] == 1 else std
+            return y_mean, y_std
+        return y_mean
+
+    def sample_y(self, X, n_samples=1, random_state=0):
+        rng = check_random_state(random_state)
+        y_mean, y_cov = self.predict(X, return_cov=True)
+        if y_mean.ndim == 1:
+            return rng.multivariate_normal(y_mean, y_cov, n_samples).T
+        return np.hstack([rng.multivariate_normal(y_mean[:, t], y_cov[..., t], n_samples).T[:, np.newaxis]
+                          for t in range(y_mean.shape[1])])
+
+    # ------------------------------------------------------------------------------------------
+    def log_marginal_likelihood(self, theta=None, eval_gradient=False, clone_kernel=True):
+        if theta is None:
+            if eval_gradient:
+                raise ValueError("Gradient can only be evaluated for theta!=None")
+            return self.log_marginal_likelihood_value_
+        if clone_kernel:
+            kernel = self.kernel_.clone_with_theta(theta)
+        else:
+            kernel = self.kernel_
+            kernel.theta = theta
+        low = lower(kernel, self.X_train_.shape[1])
+        eng = self._engine_for_training()
+        lml, g_c, g_ls, g_noise = eng.lml(1.0 / low.length_scale, low.c, low.noise, eval_gradient)
+        if eval_gradient:
+            if not np.isfinite(lml):
+                return -np.inf, np.zeros_like(np.asarray(theta, dtype=np.float64))
+            return lml, assemble_gradient(low, g_c, g_ls, g_noise)
+        return lml
+
+    def _constrained_optimization(self, obj_func, initial_theta, bounds):
+        if self.optimizer == "fmin_l_bfgs_b":
+            opt_res = scipy.optimize.minimize(obj_func, initial_theta, method="L-BFGS-B", jac=True, bounds=bounds)
+            _check_optimize_result("lbfgs", opt_res)
+            theta_opt, func_min = opt_res.x, opt_res.fun
+        elif callable(self.optimizer):
+            theta_opt, func_min = self.optimizer(obj_func, initial_theta, bounds=bounds)
+        else:
+            raise ValueError(f"Unknown optimizer {self.optimizer}.")
+        return theta_opt, func_min
+
+    # -- pickling: host NumPy only, device state rebuilt lazily ----------------------------------
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        fitted = "X_train_" in state
+        state.pop("_engine", None)
+        state.pop("_low", None)
+        L = state.pop("_L_cache", None)
+        if fitted:
+            state["L_"] = L if L is not None else self.L_
+        return state
+
+    def __setstate__(self, state):
+        L = state.pop("L_", None)
+        self.__dict__.update(state)
+        if L is not None:
+            self.__dict__["_L_cache"] = L
+        self._engine = None
+        self._low = None
+
+    @classmethod
+    def from_sklearn(cls, skl):
+        """Adopt a fitted sklearn GaussianProcessRegressor (e.g. from a reference pickle) onto the GPU."""
+        est = cls(kernel=skl.kernel, alpha=skl.alpha, optimizer=skl.optimizer,
+                  n_restarts_optimizer=skl.n_restarts_optimizer, normalize_y=skl.normalize_y,
+                  copy_X_train=skl.copy_X_train, n_targets=getattr(skl, "n_targets", None),
+                  random_state=skl.random_state)
+        for name in ("kernel_", "X_train_", "y_train_", "_y_train_mean", "_y_train_std",
+                     "log_marginal_likelihood_value_", "n_features_in_", "alpha_"):
+            if hasattr(skl, name):
+                setattr(est, name, getattr(skl, name))
+        est._engine = None
+        est._low = None
+        return est
