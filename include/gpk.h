@@ -83,6 +83,12 @@ int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* 
 /* register-resident DMMA loop for the FP64 tensor peak; returns flops executed in *flops_h */
 int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream);
 
+/* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
+ * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */
+unsigned long long gpk_launch_count(void);
+int gpk_profile_begin(void);
+int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h);
+
 #ifdef __cplusplus
 }
 #endif

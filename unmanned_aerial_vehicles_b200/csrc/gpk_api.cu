@@ -21,6 +21,10 @@ cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t
 cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
 cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
 
+unsigned long long g_gpk_launches = 0;
+GpkProfile g_gpk_prof = {0, 0, 0.0};
+double gpk_profile_collect();
+
 static int make_params(GpkKernelParams& p, int D, const double* inv_ls_h, double c, double noise, double jitter) {
   if (D < 1 || D > GPK_MAXD) return -1;
   memset(&p, 0, sizeof(p));
@@ -151,6 +155,17 @@ int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void*
   GPK_CHECK(gpk_launch_dmma_probe(blocks, iters, sink_d, (cudaStream_t)stream));
   // 256 threads = 8 warps, 16 independent m8n8k4 accumulators per warp, 512 flops each
   if (flops_h) *flops_h = (double)blocks * 8.0 * 16.0 * 512.0 * (double)iters;
+  return 0;
+}
+
+unsigned long long gpk_launch_count(void) { return g_gpk_launches; }
+int gpk_profile_begin(void) { g_gpk_prof.enabled = 1; g_gpk_prof.n = 0; g_gpk_prof.flops = 0.0; return 0; }
+int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1000;
+  if (gemm_seconds_h) *gemm_seconds_h = gpk_profile_collect();
+  if (gemm_flops_h) *gemm_flops_h = g_gpk_prof.flops;
+  if (n_launches_h) *n_launches_h = g_gpk_prof.n;
+  g_gpk_prof.enabled = 0;
   return 0;
 }
 

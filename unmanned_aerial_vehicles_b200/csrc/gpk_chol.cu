@@ -85,7 +85,7 @@ struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info;
 static void chol_rec(CholCtx& c, int off, int n) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
-    gpk_leaf_potrf_inv_kernel<<<1, 256, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info);
+    gpk_leaf_potrf_inv_kernel<<<1, 256, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info); GPK_LAUNCHED();
     c.err = cudaGetLastError();
     return;
   }
@@ -176,7 +176,7 @@ cudaError_t gpk_launch_trimv(const double* Mt, int ldm, int NP, const double* v,
                              int upper, int T, cudaStream_t st) {
   int blocks = (NP * 32 + 255) / 256;
   for (int t0 = 0; t0 < T; t0 += 4) {
-    gpk_trimv_kernel<4><<<blocks, 256, 0, st>>>(Mt, ldm, NP, v, ldv, out, ldo, upper, t0, T);
+    gpk_trimv_kernel<4><<<blocks, 256, 0, st>>>(Mt, ldm, NP, v, ldv, out, ldo, upper, t0, T); GPK_LAUNCHED();
   }
   return cudaGetLastError();
 }

@@ -47,4 +47,9 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st);
 cudaError_t gpk_launch_copy_block(const double* src, int lds, double* dst, int ldd, int rows, int cols, cudaStream_t st);
 cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, int ldd, int rows, int cols, cudaStream_t st);
 
+extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)
+#define GPK_LAUNCHED() (++g_gpk_launches)
+// optional per-launch timing of the DMMA GEMM (bench.py roofline): event pairs around each launch
+struct GpkProfile { int enabled; int n; double flops; };
+extern GpkProfile g_gpk_prof;
 #define GPK_CHECK(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return (int)(-1000 - (int)e__); } while (0)

@@ -11,6 +11,8 @@
 #define GEMM_THREADS 256
 #define STAGE_DOUBLES (2 * GPK_TILE * LDSM)
 #define GEMM_SMEM_BYTES (STAGES * STAGE_DOUBLES * 8)
+#define GPK_PROF_CAP 16384
+static cudaEvent_t g_ev0[GPK_PROF_CAP], g_ev1[GPK_PROF_CAP];
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
   unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -141,8 +143,41 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
   if (g.M <= 0 || g.N <= 0) return cudaSuccess;
   if ((g.M % GPK_TILE) || (g.N % GPK_TILE) || (g.K % GPK_TILE)) return cudaErrorInvalidValue;
   dim3 grid(g.N / GPK_TILE, g.M / GPK_TILE);
+  const bool prof = g_gpk_prof.enabled && g_gpk_prof.n < GPK_PROF_CAP;
+  if (prof) {
+    if (!g_ev0[g_gpk_prof.n]) { cudaEventCreate(&g_ev0[g_gpk_prof.n]); cudaEventCreate(&g_ev1[g_gpk_prof.n]); }
+    cudaEventRecord(g_ev0[g_gpk_prof.n], st);
+  }
   gpk_gemm_nt_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g);
+  GPK_LAUNCHED();
+  if (prof) {
+    cudaEventRecord(g_ev1[g_gpk_prof.n], st);
+    // executed tile flops: 2*128*128*(trimmed k range) summed over launched tiles
+    double fl = 0.0;
+    for (int tm = 0; tm < g.M / GPK_TILE; ++tm)
+      for (int tn = 0; tn < g.N / GPK_TILE; ++tn) {
+        if (g.lower_only && tn > tm) continue;
+        int kb = 0, ke = g.K, m0 = tm * GPK_TILE, n0 = tn * GPK_TILE;
+        if (g.a_tri == GPK_TRI_LOWER) ke = ke < m0 + GPK_TILE ? ke : m0 + GPK_TILE;
+        if (g.a_tri == GPK_TRI_UPPER) kb = kb > m0 ? kb : m0;
+        if (g.b_tri == GPK_TRI_LOWER) ke = ke < n0 + GPK_TILE ? ke : n0 + GPK_TILE;
+        if (g.b_tri == GPK_TRI_UPPER) kb = kb > n0 ? kb : n0;
+        if (ke > kb) fl += 2.0 * GPK_TILE * GPK_TILE * (double)(ke - kb);
+      }
+    g_gpk_prof.flops += fl;
+    ++g_gpk_prof.n;
+  }
   return cudaGetLastError();
+}
+
+// sum of the recorded GEMM launch durations (seconds); stream must be idle (caller synchronises)
+double gpk_profile_collect() {
+  double s = 0.0;
+  for (int i = 0; i < g_gpk_prof.n; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_ev0[i], g_ev1[i]) == cudaSuccess) s += ms * 1e-3;
+  }
+  return s;
 }
 
 // ---- small data-movement helpers ---------------------------------------------------------
@@ -158,7 +193,7 @@ cudaError_t gpk_launch_copy_block(const double* src, int lds, double* dst, int l
                                   cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   dim3 grid((cols / 2 + 255) / 256, rows);
-  gpk_copy_block_kernel<<<grid, 256, 0, st>>>(src, lds, dst, ldd, rows, cols);
+  gpk_copy_block_kernel<<<grid, 256, 0, st>>>(src, lds, dst, ldd, rows, cols); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
@@ -174,7 +209,7 @@ cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, 
                                        cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   dim3 grid(cols / 32, rows / 32), block(32, 8);
-  gpk_transpose_block_kernel<<<grid, block, 0, st>>>(src, lds, dst, ldd, rows, cols);
+  gpk_transpose_block_kernel<<<grid, block, 0, st>>>(src, lds, dst, ldd, rows, cols); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
@@ -194,6 +229,6 @@ __global__ void __launch_bounds__(256) gpk_dmma_probe_kernel(int iters, double* 
   if (s == 12345.678) sink[0] = s;  // keep the chain alive
 }
 cudaError_t gpk_launch_dmma_probe(int blocks, int iters, double* sink, cudaStream_t st) {
-  gpk_dmma_probe_kernel<<<blocks, 256, 0, st>>>(iters, sink);
+  gpk_dmma_probe_kernel<<<blocks, 256, 0, st>>>(iters, sink); GPK_LAUNCHED();
   return cudaGetLastError();
 }

@@ -255,7 +255,7 @@ cudaError_t gpk_launch_gram(const double* X, int N, int D, const GpkKernelParams
                             int lower_only, cudaStream_t st) {
   dim3 grid(NP / KTILE, NP / KTILE);
 #define CALL(DPV) gpk_gram_kernel<DPV><<<grid, 256, 0, st>>>(X, D, N, NP, p, K, NP, lower_only)
-  DISPATCH_DP(D, CALL);
+  DISPATCH_DP(D, CALL); GPK_LAUNCHED();
 #undef CALL
   return cudaGetLastError();
 }
@@ -264,7 +264,7 @@ cudaError_t gpk_launch_cross_gram(const double* Xq, int Mq, const double* X, int
                                   double* Ks, int MP, int NP, cudaStream_t st) {
   dim3 grid(NP / KTILE, MP / KTILE);
 #define CALL(DPV) gpk_cross_gram_kernel<DPV><<<grid, 256, 0, st>>>(Xq, D, Mq, X, D, N, p, Ks, NP)
-  DISPATCH_DP(D, CALL);
+  DISPATCH_DP(D, CALL); GPK_LAUNCHED();
 #undef CALL
   return cudaGetLastError();
 }
@@ -280,36 +280,36 @@ cudaError_t gpk_launch_lml_grad(const double* X, int N, int D, const GpkKernelPa
     for (int t0 = 0; t0 < T; t0 += GRAD_TC) {
       const int tc = (T - t0 < GRAD_TC) ? (T - t0) : GRAD_TC;
 #define CALL(DPV) gpk_grad_kernel<DPV><<<grid, 256, 0, st>>>(X, D, N, p, alpha + t0, T, tc, Kinv, NP, ws, t0 > 0)
-      DISPATCH_DP(D, CALL);
+      DISPATCH_DP(D, CALL); GPK_LAUNCHED();
 #undef CALL
     }
   }
-  gpk_lml_finalize_kernel<<<1, 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out);
+  gpk_lml_finalize_kernel<<<1, 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
 cudaError_t gpk_launch_predict_mean(const double* Ks, int Mq, int N, int NP, const double* alpha, int T,
                                     const double* y_mean, const double* y_std, double* mean, cudaStream_t st) {
   int blocks = (int)(((size_t)Mq * 32 + 255) / 256);
-  gpk_predict_mean_kernel<<<blocks, 256, 0, st>>>(Ks, NP, Mq, N, alpha, T, T, y_mean, y_std, mean, T);
+  gpk_predict_mean_kernel<<<blocks, 256, 0, st>>>(Ks, NP, Mq, N, alpha, T, T, y_mean, y_std, mean, T); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
 cudaError_t gpk_launch_predict_std(const double* rowsq, int ntiles, int Mq, double prior, const double* y_std, int T,
                                    double* std_out, int* neg, cudaStream_t st) {
-  gpk_predict_std_kernel<<<(Mq + 255) / 256, 256, 0, st>>>(rowsq, ntiles, Mq, prior, y_std, T, std_out, T, neg);
+  gpk_predict_std_kernel<<<(Mq + 255) / 256, 256, 0, st>>>(rowsq, ntiles, Mq, prior, y_std, T, std_out, T, neg); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
 cudaError_t gpk_launch_extract_lower(const double* src, int NP, double* dst, int N, cudaStream_t st) {
   dim3 grid((N + 255) / 256, N);
-  gpk_extract_lower_kernel<<<grid, 256, 0, st>>>(src, NP, dst, N);
+  gpk_extract_lower_kernel<<<grid, 256, 0, st>>>(src, NP, dst, N); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
 cudaError_t gpk_launch_pad_copy(const double* src, int R, int C, double* dst, int RP, int CP, cudaStream_t st) {
   dim3 grid((CP + 127) / 128, RP);
-  gpk_pad_copy_kernel<<<grid, 128, 0, st>>>(src, C, R, C, dst, CP, RP, CP);
+  gpk_pad_copy_kernel<<<grid, 128, 0, st>>>(src, C, R, C, dst, CP, RP, CP); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
@@ -318,6 +318,6 @@ __global__ void gpk_copy_diag_kernel(const double* __restrict__ A, int lda, int 
   if (i < n) d[i] = A[(size_t)i * lda + i];
 }
 cudaError_t gpk_launch_copy_diag(const double* A, int lda, int n, double* d, cudaStream_t st) {
-  gpk_copy_diag_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, d);
+  gpk_copy_diag_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, d); GPK_LAUNCHED();
   return cudaGetLastError();
 }
