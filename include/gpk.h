@@ -77,7 +77,9 @@ int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, in
 /* utilities */
 int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream);
 int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream);
-/* C (+)= alpha * A * B^T on the FP64 tensor pipe; M,N,K multiples of 128.  tri: 0 none, 1 lower, 2 upper */
+/* C (+)= alpha * A * B^T on the FP64 tensor pipe; M,N,K multiples of 128.  tri: 0 none, 1 lower, 2 upper
+ * (k-range trimming; the operand's zero triangle must hold zeros inside its diagonal 128-blocks).
+ * lower_only: every element with col <= row is produced, 128-tiles strictly above the diagonal are untouched. */
 int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* C_d, int ldc, int M, int N, int K,
                 double alpha, int accumulate, int a_tri, int b_tri, int lower_only, void* stream);
 /* register-resident DMMA loop for the FP64 tensor peak; returns flops executed in *flops_h */
@@ -88,6 +90,8 @@ int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void*
 unsigned long long gpk_launch_count(void);
 int gpk_profile_begin(void);
 int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h);
+/* after gpk_profile_end: duration, executed flops and (M,N,K) of the i-th recorded GEMM launch */
+int gpk_profile_launch(int i, double* seconds_h, double* flops_h, int* mnk_h);
 
 #ifdef __cplusplus
 }

@@ -39,10 +39,11 @@ def _data(n, d, t, seed=0):
 # ---------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("a_tri,b_tri,lower_only,acc", [(0, 0, 0, 0), (0, 1, 0, 0), (2, 0, 0, 0), (1, 0, 0, 0),
                                                         (2, 2, 1, 0), (0, 0, 1, 1)])
-def test_gemm_nt(a_tri, b_tri, lower_only, acc):
+@pytest.mark.parametrize("size", [384, 1024, 2048])
+def test_gemm_nt(a_tri, b_tri, lower_only, acc, size):
     lib = _lib.load()
     rng = np.random.default_rng(1)
-    M = N = K = 384
+    M = N = K = size
     A = rng.standard_normal((M, K)); B = rng.standard_normal((N, K)); C0 = rng.standard_normal((M, N))
     if a_tri == 1: A = np.tril(A)
     if a_tri == 2: A = np.triu(A)
@@ -53,11 +54,12 @@ def test_gemm_nt(a_tri, b_tri, lower_only, acc):
     assert rc == 0
     got = Cd.cpu().numpy()
     ref = -0.5 * (A @ B.T) + (C0 if acc else 0.0)
-    if lower_only:  # tiles strictly above the diagonal are untouched
+    if lower_only:  # contract: every element with col <= row is produced; 128-tiles strictly above are untouched
+        np.testing.assert_allclose(np.tril(got), np.tril(ref), rtol=0, atol=1e-11)
         for i in range(0, M, 128):
-            for j in range(0, N, 128):
+            for j in range(i + 128, N, 128):
                 blk = (slice(i, i + 128), slice(j, j + 128))
-                np.testing.assert_allclose(got[blk], ref[blk] if j <= i else C0[blk], rtol=0, atol=1e-11)
+                np.testing.assert_array_equal(got[blk], C0[blk])
     else:
         np.testing.assert_allclose(got, ref, rtol=0, atol=1e-11)
 

@@ -24,6 +24,7 @@ cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
 unsigned long long g_gpk_launches = 0;
 GpkProfile g_gpk_prof = {0, 0, 0.0};
 double gpk_profile_collect();
+int gpk_profile_launch_info(int, double*, double*, int*);
 
 static int make_params(GpkKernelParams& p, int D, const double* inv_ls_h, double c, double noise, double jitter) {
   if (D < 1 || D > GPK_MAXD) return -1;
@@ -159,6 +160,7 @@ int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void*
 }
 
 unsigned long long gpk_launch_count(void) { return g_gpk_launches; }
+int gpk_profile_launch(int i, double* seconds_h, double* flops_h, int* mnk_h) { return gpk_profile_launch_info(i, seconds_h, flops_h, mnk_h); }
 int gpk_profile_begin(void) { g_gpk_prof.enabled = 1; g_gpk_prof.n = 0; g_gpk_prof.flops = 0.0; return 0; }
 int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h) {
   if (cudaDeviceSynchronize() != cudaSuccess) return -1000;

@@ -12,72 +12,98 @@
 //   rec(11);  L21 = A21 * M11^T;  A22 -= L21 L21^T;  rec(22);  M21 = -M22 * L21 * M11.
 #include "gpk_common.cuh"
 
-#define LEAF_LD 129
-#define LEAF_SMEM_BYTES ((GPK_TILE * LEAF_LD + GPK_TILE) * 8)
+#define LEAF_SMEM_BYTES 0
 
-// One CTA factors a 128x128 diagonal block in shared memory and inverts the factor.
-// info: first failing global pivot index + 1 (LAPACK convention), 0 if none (atomicMin on nonzero).
+// One CTA factors a 128x128 diagonal block and inverts the factor in the same sweep.
+// The block lives in REGISTERS: 16x16 threads, thread (ty,tx) owns S[ty+16a][tx+16b], a,b < 8 (2-D cyclic).
+// Step j (one __syncthreads each, buffers double-buffered):
+//   column j (raw) and row j (raw) are published to shared memory; d = sqrt(pivot);
+//   for every row i > j and column c <= i:   c > j : A-part   S[i][c] -= l_ij * l_cj
+//                                            c < j : M-part   S[i][c] -= l_ij * M[j][c]
+//                                            c = j :          S[i][j]  = -l_ij / d
+//   i.e. forward elimination applied to [A | I] at once, so S ends as L^-1 while column j of L is streamed out.
+// info: first failing global pivot index + 1 (LAPACK convention), 0 if none.
 __global__ void __launch_bounds__(256, 1)
 gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ Mlow, double* __restrict__ Mup,
                           int ldm, int off, int* __restrict__ info) {
-  extern __shared__ double sm[];
-  double* T = sm;                          // [128][129]
-  double* dinv = sm + GPK_TILE * LEAF_LD;  // [128]
-  const int tid = threadIdx.x;
-  const int n = GPK_TILE;
+  __shared__ double colbuf[2][GPK_TILE], rowbuf[2][GPK_TILE];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   double* Ab = A + (size_t)off * lda + off;
-  for (int idx = tid; idx < n * n; idx += 256) {
-    int r = idx >> 7, c = idx & 127;
-    T[r * LEAF_LD + c] = (c <= r) ? Ab[(size_t)r * lda + c] : 0.0;
-  }
-  __syncthreads();
-  // right-looking unblocked Cholesky; thread (tid & 127) owns a row, (tid >> 7) a column parity
-  const int row = tid & 127, par = tid >> 7;
-  for (int j = 0; j < n; ++j) {
-    double d = T[j * LEAF_LD + j];
+  double S[8][8];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int i = ty + 16 * a, c = tx + 16 * b;
+      S[a][b] = (c <= i) ? Ab[(size_t)i * lda + c] : 0.0;
+    }
+  for (int j = 0; j < GPK_TILE; ++j) {
+    const int p = j & 1, bj = j >> 4, tj = j & 15;
+    if (tx == tj) {
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        double v = 0.0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) if (b == bj) v = S[a][b];
+        const int i = ty + 16 * a;
+        if (i >= j) colbuf[p][i] = v;
+      }
+    }
+    if (ty == tj) {
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        double v = 0.0;
+#pragma unroll
+        for (int a = 0; a < 8; ++a) if (a == bj) v = S[a][b];
+        const int c = tx + 16 * b;
+        if (c < j) rowbuf[p][c] = v;
+      }
+    }
+    __syncthreads();
+    double d = colbuf[p][j];
     if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
       if (tid == 0) { int want = off + j + 1; int old = atomicCAS(info, 0, want); if (old != 0 && old > want) atomicMin(info, want); }
       d = __longlong_as_double(0x7ff8000000000000LL);
     }
-    d = sqrt(d);
-    __syncthreads();
-    if (par == 0) {
-      if (row == j) T[j * LEAF_LD + j] = d;
-      else if (row > j) T[row * LEAF_LD + j] /= d;
+    const double ljj = sqrt(d), dinv = 1.0 / ljj;
+    double v[8];
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int c = tx + 16 * b;
+      v[b] = ((c < j) ? rowbuf[p][c] : colbuf[p][c]) * dinv;   // c == j handled below
     }
-    __syncthreads();
-    if (row > j) {
-      double lij = T[row * LEAF_LD + j];
-      for (int k = j + 1 + par; k <= row; k += 2) T[row * LEAF_LD + k] -= lij * T[k * LEAF_LD + j];
-    }
-    __syncthreads();
-  }
-  // write L (explicit zeros above the diagonal)
-  for (int idx = tid; idx < n * n; idx += 256) {
-    int r = idx >> 7, c = idx & 127;
-    Ab[(size_t)r * lda + c] = (c <= r) ? T[r * LEAF_LD + c] : 0.0;
-  }
-  if (tid < n) dinv[tid] = 1.0 / T[tid * LEAF_LD + tid];
-  __syncthreads();
-  // inverse: thread j solves L m_j = e_j; M[i][j] (i > j) is stored transposed in T's upper triangle
-  if (tid < n) {
-    const int j = tid;
-    for (int i = j + 1; i < n; ++i) {
-      double s = T[i * LEAF_LD + j] * dinv[j];
-      for (int k = j + 1; k < i; ++k) s += T[i * LEAF_LD + k] * T[j * LEAF_LD + k];
-      T[j * LEAF_LD + i] = -s * dinv[i];
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+      const int i = ty + 16 * a;
+      if (i > j) {
+        const double li = colbuf[p][i] * dinv;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          const int c = tx + 16 * b;
+          if (c <= i) S[a][b] = (c == j) ? (-li * dinv) : (S[a][b] - li * v[b]);
+        }
+        if (tx == tj) Ab[(size_t)i * lda + j] = li;          // column j of L
+      } else if (i == j) {                                  // row j of M becomes final
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          const int c = tx + 16 * b;
+          if (c < j) S[a][b] *= dinv;
+          else if (c == j) { S[a][b] = dinv; Ab[(size_t)j * lda + j] = ljj; }
+        }
+      }
     }
   }
-  __syncthreads();
   double* Ml = Mlow + (size_t)off * ldm + off;
   double* Mu = Mup + (size_t)off * ldm + off;
-  for (int idx = tid; idx < n * n; idx += 256) {
-    int r = idx >> 7, c = idx & 127;
-    double lo = (c < r) ? T[c * LEAF_LD + r] : (c == r ? dinv[r] : 0.0);  // M[r][c]
-    double up = (c > r) ? T[r * LEAF_LD + c] : (c == r ? dinv[r] : 0.0);  // M[c][r]
-    Ml[(size_t)r * ldm + c] = lo;
-    Mu[(size_t)r * ldm + c] = up;
-  }
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int i = ty + 16 * a, c = tx + 16 * b;
+      const double m = (c <= i) ? S[a][b] : 0.0;
+      Ml[(size_t)i * ldm + c] = m;
+      Mu[(size_t)c * ldm + i] = m;
+    }
 }
 
 struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err; };
@@ -124,13 +150,6 @@ static void chol_rec(CholCtx& c, int off, int n) {
 
 cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
                                  cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gpk_leaf_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         LEAF_SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   if (NP % GPK_TILE) return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;

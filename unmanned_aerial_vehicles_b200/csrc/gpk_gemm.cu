@@ -9,10 +9,11 @@
 #define LDSM 20               // padded smem row stride in doubles (conflict-free 8x4 fragment reads)
 #define STAGES 3
 #define GEMM_THREADS 256
-#define STAGE_DOUBLES (2 * GPK_TILE * LDSM)
-#define GEMM_SMEM_BYTES (STAGES * STAGE_DOUBLES * 8)
+#define GEMM_SMEM_BYTES_TS(TS) (STAGES * 2 * (TS) * LDSM * 8)
 #define GPK_PROF_CAP 16384
 static cudaEvent_t g_ev0[GPK_PROF_CAP], g_ev1[GPK_PROF_CAP];
+static int g_shape[GPK_PROF_CAP][3];
+static double g_lflops[GPK_PROF_CAP];
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
   unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -27,47 +28,59 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+template <int TS, int NTHR>
 __device__ __forceinline__ void load_stage(double* sA, double* sB, const double* __restrict__ A, int lda,
                                            const double* __restrict__ B, int ldb, int m0, int n0, int k0,
                                            int tid) {
-  // 128 rows x 16 doubles = 1024 16-byte chunks per operand; 4 per thread per operand
+  // TS rows x 16 doubles = TS*8 16-byte chunks per operand
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int chunk = tid + i * GEMM_THREADS;
+  for (int i = 0; i < TS * 8 / NTHR; ++i) {
+    int chunk = tid + i * NTHR;
     int r = chunk >> 3, c = (chunk & 7) * 2;
     cp_async16(sA + r * LDSM + c, A + (size_t)(m0 + r) * lda + k0 + c);
     cp_async16(sB + r * LDSM + c, B + (size_t)(n0 + r) * ldb + k0 + c);
   }
 }
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1) gpk_gemm_nt_kernel(GpkGemmArgs g) {
+// TS: CTA tile edge (128 / 64 / 32); WR x WC warps, warp tile (TS/WR) x (TS/WC)
+template <int TS, int WR, int WC>
+__global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt_kernel(GpkGemmArgs g) {
+  constexpr int NTHR = 32 * WR * WC, MT = TS / WR / 8, NT = TS / WC / 8, STAGE_DOUBLES = 2 * TS * LDSM;
   extern __shared__ __align__(16) double smem[];
-  const int tn = blockIdx.x, tm = blockIdx.y;
+  // grouped raster: 8 tile-rows per group, column-major inside a group, so co-resident CTAs share A and B panels in L2
+  int tn, tm;
+  {
+    const int ntn = gridDim.x, ntm = gridDim.y, id = blockIdx.y * ntn + blockIdx.x;
+    const int grp = id / (8 * ntn), within = id - grp * 8 * ntn;
+    const int gsz = min(8, ntm - grp * 8);
+    tm = grp * 8 + within % gsz;
+    tn = within / gsz;
+  }
   if (g.lower_only && tn > tm) return;
-  const int m0 = tm * GPK_TILE, n0 = tn * GPK_TILE;
+  const int m0 = tm * TS, n0 = tn * TS;
   int kb = 0, ke = g.K;
-  if (g.a_tri == GPK_TRI_LOWER) ke = min(ke, m0 + GPK_TILE);
+  if (g.a_tri == GPK_TRI_LOWER) ke = min(ke, m0 + TS);
   if (g.a_tri == GPK_TRI_UPPER) kb = max(kb, m0);
-  if (g.b_tri == GPK_TRI_LOWER) ke = min(ke, n0 + GPK_TILE);
+  if (g.b_tri == GPK_TRI_LOWER) ke = min(ke, n0 + TS);
   if (g.b_tri == GPK_TRI_UPPER) kb = max(kb, n0);
   const int nk = (ke > kb) ? (ke - kb) / KT : 0;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+  const int wm = (warp / WC) * (TS / WR), wn = (warp % WC) * (TS / WC);
   const int fr = lane >> 2, fk = lane & 3;
 
-  double acc[8][4][2];
+  double acc[MT][NT][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < MT; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
   // prologue
 #pragma unroll
   for (int s = 0; s < STAGES - 1; ++s) {
     if (s < nk) {
       double* sA = smem + s * STAGE_DOUBLES;
-      load_stage(sA, sA + GPK_TILE * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + s * KT, tid);
+      load_stage<TS, NTHR>(sA, sA + TS * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + s * KT, tid);
     }
     cp_async_commit();
   }
@@ -78,33 +91,33 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gpk_gemm_nt_kernel(GpkGemmArg
       int nxt = kt + STAGES - 1;
       if (nxt < nk) {
         double* sA = smem + (nxt % STAGES) * STAGE_DOUBLES;
-        load_stage(sA, sA + GPK_TILE * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + nxt * KT, tid);
+        load_stage<TS, NTHR>(sA, sA + TS * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + nxt * KT, tid);
       }
       cp_async_commit();
     }
     const double* sA = smem + (kt % STAGES) * STAGE_DOUBLES;
-    const double* sB = sA + GPK_TILE * LDSM;
+    const double* sB = sA + TS * LDSM;
 #pragma unroll
     for (int kk = 0; kk < KT; kk += 4) {
-      double a[8], b[4];
+      double a[MT], b[NT];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) a[i] = sA[(wm + i * 8 + fr) * LDSM + kk + fk];
+      for (int i = 0; i < MT; ++i) a[i] = sA[(wm + i * 8 + fr) * LDSM + kk + fk];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = sB[(wn + j * 8 + fr) * LDSM + kk + fk];
+      for (int j = 0; j < NT; ++j) b[j] = sB[(wn + j * 8 + fr) * LDSM + kk + fk];
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < MT; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
   }
   cp_async_wait<0>();
 
   if (g.epilogue == GPK_EPI_STORE) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < MT; ++i) {
       int row = m0 + wm + i * 8 + fr;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < NT; ++j) {
         int col = n0 + wn + j * 8 + fk * 2;
         double2* p = reinterpret_cast<double2*>(g.C + (size_t)row * g.ldc + col);
         double2 v = make_double2(g.alpha * acc[i][j][0], g.alpha * acc[i][j][1]);
@@ -112,17 +125,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gpk_gemm_nt_kernel(GpkGemmArg
         *p = v;
       }
     }
-  } else {  // GPK_EPI_ROWSUMSQ: rowsq[row, tn] = sum_n (alpha*acc)^2 over this tile's 128 columns
+  } else if (TS == 128) {  // GPK_EPI_ROWSUMSQ: rowsq[row, tn] = sum_n (alpha*acc)^2 over this tile's 128 columns
     __syncthreads();
     double* red = smem;  // [128][4]
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < MT; ++i) {
       double s = 0.0;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) s += acc[i][j][0] * acc[i][j][0] + acc[i][j][1] * acc[i][j][1];
+      for (int j = 0; j < NT; ++j) s += acc[i][j][0] * acc[i][j][0] + acc[i][j][1] * acc[i][j][1];
       s += __shfl_xor_sync(0xffffffffu, s, 1);
       s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (fk == 0) red[(wm + i * 8 + fr) * 4 + (warp & 3)] = s;
+      if (fk == 0) red[(wm + i * 8 + fr) * 4 + (warp % WC)] = s;
     }
     __syncthreads();
     if (tid < GPK_TILE) {
@@ -132,23 +145,34 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gpk_gemm_nt_kernel(GpkGemmArg
   }
 }
 
-cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
+template <int TS, int WR, int WC>
+static cudaError_t launch_ts(const GpkGemmArgs& g, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gpk_gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         GEMM_SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gpk_gemm_nt_kernel<TS, WR, WC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         GEMM_SMEM_BYTES_TS(TS));
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
+  dim3 grid(g.N / TS, g.M / TS);
+  gpk_gemm_nt_kernel<TS, WR, WC><<<grid, 32 * WR * WC, GEMM_SMEM_BYTES_TS(TS), st>>>(g);
+  return cudaGetLastError();
+}
+
+cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
   if (g.M <= 0 || g.N <= 0) return cudaSuccess;
   if ((g.M % GPK_TILE) || (g.N % GPK_TILE) || (g.K % GPK_TILE)) return cudaErrorInvalidValue;
-  dim3 grid(g.N / GPK_TILE, g.M / GPK_TILE);
+  // tile size by available parallelism: small problems are split finer so they cover more of the 148 SMs
+  const long t128 = (long)(g.M / 128) * (g.N / 128);
+  int ts = 128;
+  if (g.epilogue == GPK_EPI_STORE) { if (t128 < 16) ts = 32; else if (t128 < 100) ts = 64; }
   const bool prof = g_gpk_prof.enabled && g_gpk_prof.n < GPK_PROF_CAP;
   if (prof) {
     if (!g_ev0[g_gpk_prof.n]) { cudaEventCreate(&g_ev0[g_gpk_prof.n]); cudaEventCreate(&g_ev1[g_gpk_prof.n]); }
     cudaEventRecord(g_ev0[g_gpk_prof.n], st);
   }
-  gpk_gemm_nt_kernel<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(g);
+  cudaError_t le = ts == 128 ? launch_ts<128, 2, 4>(g, st) : ts == 64 ? launch_ts<64, 2, 2>(g, st) : launch_ts<32, 2, 2>(g, st);
+  if (le != cudaSuccess) return le;
   GPK_LAUNCHED();
   if (prof) {
     cudaEventRecord(g_ev1[g_gpk_prof.n], st);
@@ -165,6 +189,7 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
         if (ke > kb) fl += 2.0 * GPK_TILE * GPK_TILE * (double)(ke - kb);
       }
     g_gpk_prof.flops += fl;
+    g_lflops[g_gpk_prof.n] = fl; g_shape[g_gpk_prof.n][0] = g.M; g_shape[g_gpk_prof.n][1] = g.N; g_shape[g_gpk_prof.n][2] = g.K;
     ++g_gpk_prof.n;
   }
   return cudaGetLastError();
@@ -231,4 +256,12 @@ __global__ void __launch_bounds__(256) gpk_dmma_probe_kernel(int iters, double* 
 cudaError_t gpk_launch_dmma_probe(int blocks, int iters, double* sink, cudaStream_t st) {
   gpk_dmma_probe_kernel<<<blocks, 256, 0, st>>>(iters, sink); GPK_LAUNCHED();
   return cudaGetLastError();
+}
+
+int gpk_profile_launch_info(int i, double* seconds, double* flops, int* mnk) {
+  if (i < 0 || i >= g_gpk_prof.n) return -1;
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, g_ev0[i], g_ev1[i]);
+  *seconds = ms * 1e-3; *flops = g_lflops[i]; mnk[0] = g_shape[i][0]; mnk[1] = g_shape[i][1]; mnk[2] = g_shape[i][2];
+  return 0;
 }
