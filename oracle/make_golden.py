@@ -115,6 +115,12 @@ def main():
     np.savez_compressed(os.path.join(OUT, "lml_grid_const_ard.npz"), X=Xr, Y=Yr, theta_grid=grid,
                         lml_grid=np.array(lmls), grad_grid=np.array(grads), Xq=Xr[:50] * 1.1, mean=mq, std=sq,
                         alpha_=g.alpha_)
+    # ---- the one metrics artefact the reference committed (evaluate_gp_offline.py:277-312) ---------------
+    ds = os.path.join(REF, "gp_datasets", "gp_mpc_data_20251124_225535.csv")
+    mt = pd.read_csv(os.path.join(REF, "gp_datasets", "gp_mpc_data_20251124_225535_metrics.csv"))
+    R = pd.read_csv(ds)[RES].to_numpy(dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "metrics_nominal.npz"), R_true=R, mse_nom=mt["mse_nom"].to_numpy(),
+                        rmse_nom=mt["rmse_nom"].to_numpy(), r2_nom=mt["r2_nom"].to_numpy())
     print("done")
 
 

@@ -1,0 +1,66 @@
+"""World-size-2 gloo tests of the sharding logic (host side; the objective here is the CPU oracle because this
+container has no GPU -- the sharding code is identical on NCCL)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import scipy.optimize
+    from oracle import gp_oracle as orc
+    from unmanned_aerial_vehicles_b200 import parallel
+
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((60, 2)); y = np.sin(X[:, 0]) + 0.05 * rng.standard_normal(60)
+    calls = []
+
+    def run_one(t0):
+        calls.append(tuple(t0))
+        f = lambda th: (lambda l, g: (-l, -np.array([g["ls"].sum(), g["noise"]])))(
+            *orc.lml_and_grad(X, y, np.exp(th[0]), 1.0, np.exp(th[1]), 1e-8))
+        r = scipy.optimize.minimize(f, t0, method="L-BFGS-B", jac=True, bounds=[(-3, 3), (-8, 1)])
+        return r.x, r.fun
+    starts = [np.array([0.0, -2.0])] + [np.random.RandomState(1).uniform([-3, -8], [3, 1]) for _ in range(4)]
+    res = parallel.run_sharded(run_one, starts)
+    lo, hi = parallel.row_block(11, rank, world)
+    q.put((rank, len(calls), [(list(map(float, a)), float(b)) for a, b in res], (lo, hi)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_restarts_match_serial():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    outs = sorted(q.get(timeout=240) for _ in range(2))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    (r0, n0, res0, blk0), (r1, n1, res1, blk1) = outs
+    assert n0 == 3 and n1 == 2            # 5 runs round-robin over 2 ranks
+    assert res0 == res1 and len(res0) == 5  # every rank holds every result, in start order
+    assert blk0 == (0, 6) and blk1 == (6, 11)
+    best = int(np.argmin([f for _, f in res0]))
+    assert np.isfinite(res0[best][1])
+
+
+def test_shard_helpers_single_process():
+    from unmanned_aerial_vehicles_b200 import parallel
+    assert parallel.shard_indices(10, 1, 4) == [1, 5, 9]
+    assert [parallel.row_block(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 8), (8, 10)]
+    assert parallel.run_sharded(lambda v: v * 2, [1, 2, 3]) == [2, 4, 6]

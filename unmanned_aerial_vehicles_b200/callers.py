@@ -1,0 +1,247 @@
+"""Host-side mirrors of the reference callers either side of the hot path, each keeping the
+reference's per-row API and adding the batched form the GPU wants.
+
+  SimpleQuadrotorGP        <- src/px4/simple_gp.py:24-223      (ring buffers, filters, train_gp, predict_residual)
+  build_gp_residuals       <- src/px4/mpc.py:1475-1511          (25 sequential one-row predicts -> ONE batched call)
+  PerOutputGP              <- src/px4/pretrained_gp.py:27-98, gp_trainer.py:207-227 (schema B: per-output models
+                              + scalers), gp_enhanced_mpc.py:94-183 (schema C)
+  adopt_pickle             <- the three pickle schemas of SURVEY section 5
+  evaluate_residual_metrics<- src/px4/evaluate_gp_offline.py:186-312 (MSE/RMSE/R2/improvement/frac_better)
+  load_csv_dataset         <- src/px4/train_gp_offline.py:22-76 (vectorised: no per-row Python loop)
+"""
+from __future__ import annotations
+
+import os
+import pickle
+from collections import deque
+
+import numpy as np
+from sklearn.gaussian_process.kernels import RBF, WhiteKernel
+
+from .gpr import GaussianProcessRegressor
+
+FEATURE_COLS = ["x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az", "yaw_rate"]
+RESIDUAL_COLS = ["res_dx", "res_dy", "res_dz", "res_dvx", "res_dvy", "res_dvz"]
+
+
+def load_csv_dataset(path, max_residual_norm=5.0):
+    """(X (n,10), Y (n,6)) with the reference's row filter: finite and ||res|| < 5 (train_gp_offline.py:59-65)."""
+    import pandas as pd
+
+    df = pd.read_csv(path)
+    missing = [c for c in FEATURE_COLS + RESIDUAL_COLS if c not in df.columns]
+    if missing:
+        raise ValueError(f"Missing columns: {missing}")
+    X = df[FEATURE_COLS].to_numpy(dtype=np.float64)
+    Y = df[RESIDUAL_COLS].to_numpy(dtype=np.float64)
+    ok = np.isfinite(X).all(1) & np.isfinite(Y).all(1) & (np.linalg.norm(Y, axis=1) < max_residual_norm)
+    return X[ok], Y[ok]
+
+
+class SimpleQuadrotorGP:
+    """Same surface as the reference wrapper; the estimator underneath is the B200 one."""
+
+    def __init__(self, max_data_points=1000, random_state=None):
+        self.max_data_points = max_data_points
+        self.X_train = deque(maxlen=max_data_points)
+        self.Y_train = deque(maxlen=max_data_points)
+        self.gp_model = None
+        self.is_trained = False
+        self.training_count = 0
+        self.prediction_count = 0
+        self.random_state = random_state
+
+    # -- data ------------------------------------------------------------------------------------
+    @staticmethod
+    def _nominal_dynamics(state, control, dt):
+        state = np.asarray(state, dtype=np.float64)
+        control = np.asarray(control, dtype=np.float64)
+        return state + dt * np.concatenate([state[..., 3:6], control[..., :3]], axis=-1)
+
+    def add_training_data(self, state, control, state_next, dt=0.02):
+        if len(state) < 6 or len(state_next) < 6:
+            return
+        state, control, state_next = (np.asarray(v, dtype=np.float64) for v in (state, control, state_next))
+        if np.linalg.norm(state[3:6]) > 5.0 or np.linalg.norm(control[:3]) > 3.0:
+            return
+        residual = state_next - self._nominal_dynamics(state[:6], control, dt)
+        if np.linalg.norm(residual) > 2.0:
+            return
+        self.X_train.append(np.concatenate([state[:6], control[:4]]))
+        self.Y_train.append(residual.copy())
+
+    def extend(self, X, Y):
+        for xi, yi in zip(X, Y):
+            self.X_train.append(np.asarray(xi, dtype=np.float64))
+            self.Y_train.append(np.asarray(yi, dtype=np.float64))
+
+    def save_dataset(self, path):
+        import pandas as pd
+
+        X = np.array(self.X_train) if len(self.X_train) else np.empty((0, 10))
+        Y = np.array(self.Y_train) if len(self.Y_train) else np.empty((0, 6))
+        pd.DataFrame(np.hstack([X, Y]), columns=FEATURE_COLS + RESIDUAL_COLS).to_csv(path, index=False)
+
+    # -- train / predict -------------------------------------------------------------------------
+    def train_gp(self):
+        if len(self.X_train) < 30:
+            return
+        try:
+            X = np.array(list(self.X_train))
+            Y = np.array(list(self.Y_train))
+            kernel = RBF(length_scale=0.5) + WhiteKernel(noise_level=0.1)          # simple_gp.py:167
+            self.gp_model = GaussianProcessRegressor(kernel=kernel, alpha=1e-4, normalize_y=True,
+                                                     n_restarts_optimizer=1, random_state=self.random_state)
+            self.gp_model.fit(X, Y)
+            self.is_trained = True
+            self.training_count += 1
+        except (np.linalg.LinAlgError, ValueError) as e:  # the reference swallows and reports
+            print(f"GP training failed: {e}")
+            self.is_trained = False
+
+    def predict_residual(self, state, control):
+        """one row -> (mean (6,), variance (6,)), as simple_gp.py:187-201"""
+        if not self.is_trained:
+            return np.zeros(6), np.ones(6)
+        x = np.concatenate([state, control]).reshape(1, -1)
+        mean, std = self.gp_model.predict(x, return_std=True)
+        self.prediction_count += 1
+        return mean.flatten(), std.flatten() ** 2
+
+    def predict_residual_batch(self, states, controls, return_var=True):
+        """(M,6),(M,4) -> mean (M,T) [, variance (M,T)] in ONE device call."""
+        states = np.asarray(states, dtype=np.float64)
+        if not self.is_trained:
+            return np.zeros((len(states), 6)), np.ones((len(states), 6))
+        x = np.hstack([states, np.asarray(controls, dtype=np.float64)])
+        self.prediction_count += len(x)
+        if not return_var:
+            return np.atleast_2d(self.gp_model.predict(x)), None
+        mean, std = self.gp_model.predict(x, return_std=True)
+        return mean.reshape(len(x), -1), std.reshape(len(x), -1) ** 2
+
+    def get_uncertainty(self, state, control):
+        _, variance = self.predict_residual(state, control)
+        return float(np.mean(np.sqrt(variance)))
+
+    def predict_enhanced_dynamics(self, state, control, dt):
+        mean, _ = self.predict_residual(state, control)
+        return self._nominal_dynamics(np.asarray(state)[:6], control, dt) + mean
+
+    def load_model(self, model_path):
+        if not os.path.exists(model_path):
+            return False
+        with open(model_path, "rb") as f:
+            data = pickle.load(f)
+        model = adopt_pickle(data)
+        if isinstance(model, dict):
+            return False
+        self.gp_model = model
+        self.is_trained = True
+        if isinstance(data, dict):
+            self.training_count = data.get("training_count", 1)
+        return True
+
+    def get_stats(self):
+        return {"is_trained": self.is_trained, "data_points": len(self.X_train),
+                "training_iterations": self.training_count, "predictions_made": self.prediction_count,
+                "sklearn_available": True}
+
+
+def build_gp_residuals(gp, X_guess, U_guess, dt, gain, n_states=6):
+    """Batched QuadrotorMPC._build_gp_residuals (mpc.py:1475-1511): D (n_states, N) with rows 3:6 =
+    gain * residual_mean[3:6] / dt for the N warm-start pairs (x_k, u_k), from ONE predict call."""
+    N = U_guess.shape[1]
+    D = np.zeros((n_states, N))
+    if gp is None or not gp.is_trained:
+        return D
+    mean, _ = gp.predict_residual_batch(X_guess[:, :N].T, U_guess.T, return_var=False)
+    if mean.shape[1] >= n_states:
+        D[3:6, :] = gain * (mean[:, 3:6] / dt).T
+    return D
+
+
+def build_gp_residuals_scenarios(gp, X_guess, U_guess, dt, gain, n_states=6):
+    """Scenario form: X_guess (S, 6, N+1), U_guess (S, 4, N) -> D (S, n_states, N), one device call."""
+    S, _, N = U_guess.shape
+    xs = np.transpose(X_guess[:, :, :N], (0, 2, 1)).reshape(S * N, -1)
+    us = np.transpose(U_guess, (0, 2, 1)).reshape(S * N, -1)
+    D = np.zeros((S, n_states, N))
+    if gp is None or not gp.is_trained:
+        return D
+    mean, _ = gp.predict_residual_batch(xs, us, return_var=False)
+    D[:, 3:6, :] = gain * np.transpose((mean[:, 3:6] / dt).reshape(S, N, 3), (0, 2, 1))
+    return D
+
+
+def _to_b200(model):
+    if isinstance(model, GaussianProcessRegressor):
+        return model
+    if hasattr(model, "kernel_") and hasattr(model, "X_train_"):
+        return GaussianProcessRegressor.from_sklearn(model)
+    return model
+
+
+class PerOutputGP:
+    """Schema B/C: one single-output GP + input/output StandardScaler per residual component."""
+
+    def __init__(self, models, scalers_X, scalers_y, names=None):
+        self.names = list(names) if names is not None else list(models.keys())
+        self.models = {k: _to_b200(v) for k, v in models.items()}
+        self.scalers_X, self.scalers_y = scalers_X, scalers_y
+        self.is_loaded = True
+
+    def predict_batch(self, X, return_std=True):
+        """(M, D) -> mean (M, n_outputs), std (M, n_outputs); missing outputs give (0, 1e6) like the reference."""
+        X = np.asarray(X, dtype=np.float64)
+        M = len(X)
+        mean = np.zeros((M, len(self.names)))
+        std = np.full((M, len(self.names)), 1e6)
+        for i, name in enumerate(self.names):
+            if name not in self.models:
+                continue
+            Xs = self.scalers_X[name].transform(X)
+            sy = self.scalers_y[name]
+            if return_std:
+                m, s = self.models[name].predict(Xs, return_std=True)
+                std[:, i] = np.abs(s * sy.scale_[0])                      # pretrained_gp.py:87
+            else:
+                m = self.models[name].predict(Xs)
+            mean[:, i] = sy.inverse_transform(np.asarray(m).reshape(-1, 1)).ravel()
+        return mean, (std if return_std else None)
+
+    def predict_residual(self, state, control):
+        x = np.concatenate([np.asarray(state)[:6], np.asarray(control)[:4]]).reshape(1, -1)
+        m, s = self.predict_batch(x)
+        return m[0], s[0]
+
+
+def adopt_pickle(obj):
+    """Return a B200 estimator (schema A / bare estimator) or a PerOutputGP (schemas B, C)."""
+    if isinstance(obj, dict):
+        if "gp_model" in obj:                                                       # A: train_gp_offline.py:188
+            return _to_b200(obj["gp_model"])
+        if "gp_models" in obj:                                                      # B: gp_trainer.py:214
+            return PerOutputGP(obj["gp_models"], obj["scalers_X"], obj["scalers_y"])
+        if "models" in obj:                                                         # C: gp_enhanced_mpc.py:119
+            return PerOutputGP(obj["models"], obj["scalers_input"], obj["scalers_output"])
+        return obj
+    return _to_b200(obj)
+
+
+def evaluate_residual_metrics(Y_true, Y_gp, names=None):
+    """evaluate_gp_offline.py:277-312: per component, nominal model = zero residual."""
+    Y_true, Y_gp = np.asarray(Y_true, dtype=np.float64), np.asarray(Y_gp, dtype=np.float64)
+    names = names or ["dx", "dy", "dz", "dvx", "dvy", "dvz"][: Y_true.shape[1]]
+    rows = []
+    for j, name in enumerate(names):
+        t, g = Y_true[:, j], Y_gp[:, j]
+        mse_nom, mse_gp = float(np.mean(t ** 2)), float(np.mean((t - g) ** 2))
+        var = float(np.var(t))
+        rows.append({"component": name, "mse_nom": mse_nom, "mse_gp": mse_gp, "rmse_nom": mse_nom ** 0.5,
+                     "rmse_gp": mse_gp ** 0.5,
+                     "r2_nom": 1.0 - mse_nom / var if var > 0 else float("nan"),
+                     "r2_gp": 1.0 - mse_gp / var if var > 0 else float("nan"),
+                     "improvement_%": (mse_nom - mse_gp) / max(mse_nom, 1e-12) * 100.0,
+                     "frac_better": float(np.mean(t ** 2 > (t - g) ** 2))})
+    return rows

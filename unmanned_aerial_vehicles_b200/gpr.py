@@ -95,15 +95,20 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
                     return -lml, -grad
                 return -self.log_marginal_likelihood(theta, clone_kernel=False)
 
-            optima = [self._constrained_optimization(obj_func, self.kernel_.theta, self.kernel_.bounds)]
+            # starting points exactly as sklearn draws them (_gpr.py:312-333): kernel theta, then log-uniform
+            starts = [self.kernel_.theta]
+            bounds = self.kernel_.bounds
             if self.n_restarts_optimizer > 0:
                 if not np.isfinite(self.kernel_.bounds).all():
                     raise ValueError("Multiple optimizer restarts (n_restarts_optimizer>0) "
                                      "requires that all bounds are finite.")
-                bounds = self.kernel_.bounds
                 for _ in range(self.n_restarts_optimizer):
-                    theta_initial = self._rng.uniform(bounds[:, 0], bounds[:, 1])
-                    optima.append(self._constrained_optimization(obj_func, theta_initial, bounds))
+                    starts.append(self._rng.uniform(bounds[:, 0], bounds[:, 1]))
+            runner = getattr(self, "_restart_runner", None)
+            if runner is None:
+                optima = [self._constrained_optimization(obj_func, t0, bounds) for t0 in starts]
+            else:  # parallel.py: runs sharded over ranks, results gathered in start order
+                optima = runner(lambda t0: self._constrained_optimization(obj_func, t0, bounds), starts)
             lml_values = list(map(itemgetter(1), optima))
             self.kernel_.theta = optima[np.argmin(lml_values)][0]
             self.kernel_._check_bounds_params()
