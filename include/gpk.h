@@ -85,6 +85,17 @@ int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* 
 /* register-resident DMMA loop for the FP64 tensor peak; returns flops executed in *flops_h */
 int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream);
 
+/* building blocks of the distributed factorisation (dist_chol.py) */
+/* transpose == 0: out (M x T) = beta*out + alpha * A (M x K) v (K x T);  != 0: out (K x T) += alpha * A^T v (M x T) */
+int gpk_gemv(const double* A_d, int lda, int M, int K, const double* v_d, int T, double* out_d, double alpha, double beta,
+             int transpose, void* stream);
+/* out = tri(M) v with M (NP x NP, ld NP) lower (upper == 0) or upper; v, out (NP x T) */
+int gpk_trimv(const double* M_d, int NP, const double* v_d, double* out_d, int T, int upper, void* stream);
+/* A[i,i] += add for i < n_valid, A[i,i] = pad_value for n_valid <= i < n */
+int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pad_value, void* stream);
+/* *sum_d += sum_i log A[i,i], i < n */
+int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
+
 /* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
  * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */
 unsigned long long gpk_launch_count(void);

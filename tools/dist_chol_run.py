@@ -1,0 +1,56 @@
+"""torchrun driver for the distributed GP factorisation (BASELINE config 5).
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node P --master-addr 127.0.0.1 --master-port 29511 \
+      tools/dist_chol_run.py --n 200000 --nb 2048 [--check]
+Rank 0 prints one JSON line and appends it to gpurun_out/dist_chol.jsonl."""
+import argparse, json, os, sys, time
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from unmanned_aerial_vehicles_b200.dist_chol import DistGP
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--n", type=int, default=200000); ap.add_argument("--nb", type=int, default=2048)
+ap.add_argument("--check", action="store_true")
+a = ap.parse_args()
+world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
+torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+D, T = 9, (3 if a.n <= 50000 else 1)
+rng = np.random.default_rng(20251129)
+X = rng.standard_normal((a.n, D)); w = rng.standard_normal((D, T)) / 3
+Y = np.sin(X @ w) + 0.1 * rng.standard_normal((a.n, T))
+ls, noise, jit = np.ones(D), 0.01, 1e-6
+t0 = time.perf_counter()
+g = DistGP(X, Y, jit, NB=a.nb)
+torch.cuda.synchronize()
+if world > 1: dist.barrier()
+t1 = time.perf_counter()
+info = g.factor(1.0 / ls, 1.0, noise)
+torch.cuda.synchronize()
+if world > 1: dist.barrier()
+t2 = time.perf_counter()
+g.solve(); lml = g.lml()
+torch.cuda.synchronize()
+t3 = time.perf_counter()
+fl = torch.tensor([g.gemm_flops], dtype=torch.float64, device="cuda")
+mem = torch.tensor([torch.cuda.max_memory_allocated() / 2 ** 30], dtype=torch.float64, device="cuda")
+if world > 1:
+    dist.all_reduce(fl); dist.all_reduce(mem, op=dist.ReduceOp.MAX)
+out = {"what": "dist_chol", "n": a.n, "nb": a.nb, "n_gpus": world, "T": T, "info": info, "alloc_s": t1 - t0,
+       "assemble_factor_s": t2 - t1, "solve_lml_s": t3 - t2, "lml": lml, "potrf_alg_tflops": (a.n ** 3 / 3) / (t2 - t1) / 1e12,
+       "executed_gemm_tflops": float(fl[0]) / (t2 - t1) / 1e12, "max_mem_gib_per_gpu": float(mem[0]),
+       "local_gib": g.local_bytes() / 2 ** 30}
+if a.check and rank == 0:
+    from unmanned_aerial_vehicles_b200.engine import DeviceGP
+    eng = DeviceGP(X, Y, jit)
+    assert eng.factor(1.0 / ls, 1.0, noise) == 0
+    ref = eng.lml(1.0 / ls, 1.0, noise, False)[0]
+    eng.factor(1.0 / ls, 1.0, noise)
+    out["check_lml_rel"] = abs(lml - ref) / abs(ref)
+    out["check_alpha_maxrel"] = float(np.max(np.abs(g.alpha_host() - eng.alpha_host())) / np.max(np.abs(eng.alpha_host())))
+if rank == 0:
+    print(json.dumps(out), flush=True)
+    os.makedirs("gpurun_out", exist_ok=True)
+    open("gpurun_out/dist_chol.jsonl", "a").write(json.dumps(out) + "\n")
+if world > 1:
+    dist.barrier(); dist.destroy_process_group()

@@ -20,6 +20,10 @@ cudaError_t gpk_launch_potrf_inv(double*, int, double*, double*, int, int, int*,
 cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
 cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
+cudaError_t gpk_launch_gemv_n(const double*, int, int, int, const double*, int, double*, double, double, cudaStream_t);
+cudaError_t gpk_launch_gemv_t(const double*, int, int, int, const double*, int, double*, double, cudaStream_t);
+cudaError_t gpk_launch_fix_diag(double*, int, int, int, double, double, cudaStream_t);
+cudaError_t gpk_launch_logdiag(const double*, int, int, double*, cudaStream_t);
 
 unsigned long long g_gpk_launches = 0;
 GpkProfile g_gpk_prof = {0, 0, 0.0};
@@ -111,7 +115,7 @@ int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, 
                    double* Ks_d, int MP, int NP, void* stream) {
   GpkKernelParams p;
   if (Mq < 1) return -2; if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -5;
-  if (MP % GPK_TILE || MP < Mq) return -9; if (NP != gpk_pad(N)) return -10;
+  if (MP % 64 || MP < Mq) return -9; if (NP < N || NP % 64) return -10;
   GPK_CHECK(gpk_launch_cross_gram(Xq_d, Mq, X_d, N, D, p, Ks_d, MP, NP, (cudaStream_t)stream));
   return 0;
 }
@@ -159,6 +163,26 @@ int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void*
   return 0;
 }
 
+int gpk_gemv(const double* A_d, int lda, int M, int K, const double* v_d, int T, double* out_d, double alpha, double beta,
+             int transpose, void* stream) {
+  if (!A_d) return -1; if (T < 1) return -6;
+  if (transpose) GPK_CHECK(gpk_launch_gemv_t(A_d, lda, M, K, v_d, T, out_d, alpha, (cudaStream_t)stream));
+  else GPK_CHECK(gpk_launch_gemv_n(A_d, lda, M, K, v_d, T, out_d, alpha, beta, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_trimv(const double* M_d, int NP, const double* v_d, double* out_d, int T, int upper, void* stream) {
+  if (!M_d) return -1; if (T < 1) return -5;
+  GPK_CHECK(gpk_launch_trimv(M_d, NP, NP, v_d, T, out_d, T, upper, T, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pad_value, void* stream) {
+  GPK_CHECK(gpk_launch_fix_diag(A_d, lda, n, n_valid, add, pad_value, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream) {
+  GPK_CHECK(gpk_launch_logdiag(A_d, lda, n, sum_d, (cudaStream_t)stream));
+  return 0;
+}
 unsigned long long gpk_launch_count(void) { return g_gpk_launches; }
 int gpk_profile_launch(int i, double* seconds_h, double* flops_h, int* mnk_h) { return gpk_profile_launch_info(i, seconds_h, flops_h, mnk_h); }
 int gpk_profile_begin(void) { g_gpk_prof.enabled = 1; g_gpk_prof.n = 0; g_gpk_prof.flops = 0.0; return 0; }

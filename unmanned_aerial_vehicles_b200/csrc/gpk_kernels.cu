@@ -321,3 +321,81 @@ cudaError_t gpk_launch_copy_diag(const double* A, int lda, int n, double* d, cud
   gpk_copy_diag_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, d); GPK_LAUNCHED();
   return cudaGetLastError();
 }
+
+// ---- small dense helpers used by the distributed factorisation (dist_chol.py) -----------------
+// out[m,t] = beta*out[m,t] + alpha * sum_k A[m,k] v[k,t]; one warp per row
+__global__ void gpk_gemv_n_kernel(const double* __restrict__ A, int lda, int M, int K, const double* __restrict__ v,
+                                  int T, double* __restrict__ out, double alpha, double beta) {
+  int row = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const double* ar = A + (size_t)row * lda;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    double acc[4] = {0, 0, 0, 0};
+    for (int k = lane; k < K; k += 32) {
+      double a = ar[k];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) if (t0 + t < T) acc[t] += a * v[(size_t)k * T + t0 + t];
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      double s = acc[t];
+      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0 && t0 + t < T) {
+        double* o = out + (size_t)row * T + t0 + t;
+        *o = (beta == 0.0 ? 0.0 : beta * *o) + alpha * s;
+      }
+    }
+  }
+}
+// out[c,t] += alpha * sum_r A[r,c] v[r,t]  (out pre-zeroed by the caller when needed); atomics over row chunks
+__global__ void gpk_gemv_t_kernel(const double* __restrict__ A, int lda, int M, int K, const double* __restrict__ v,
+                                  int T, double* __restrict__ out, double alpha) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  int r0 = blockIdx.y * 512, r1 = min(M, r0 + 512);
+  if (c >= K) return;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    double acc[4] = {0, 0, 0, 0};
+    for (int r = r0; r < r1; ++r) {
+      double a = A[(size_t)r * lda + c];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) if (t0 + t < T) acc[t] += a * v[(size_t)r * T + t0 + t];
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) if (t0 + t < T) atomicAdd(out + (size_t)c * T + t0 + t, alpha * acc[t]);
+  }
+}
+// A[i,i] = (i < n_valid) ? A[i,i] + add : pad_value
+__global__ void gpk_fix_diag_kernel(double* __restrict__ A, int lda, int n, int n_valid, double add, double pad_value) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { double* p = A + (size_t)i * lda + i; *p = (i < n_valid) ? (*p + add) : pad_value; }
+}
+// s[0] += sum_i log A[i,i], i < n  (single block)
+__global__ void gpk_logdiag_kernel(const double* __restrict__ A, int lda, int n, double* __restrict__ s) {
+  __shared__ double sh[256];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) a += log(A[(size_t)i * lda + i]);
+  sh[threadIdx.x] = a; __syncthreads();
+  for (int o = 128; o; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) s[0] += sh[0];
+}
+cudaError_t gpk_launch_gemv_n(const double* A, int lda, int M, int K, const double* v, int T, double* out, double alpha,
+                              double beta, cudaStream_t st) {
+  if (M <= 0) return cudaSuccess;
+  gpk_gemv_n_kernel<<<(unsigned)(((size_t)M * 32 + 255) / 256), 256, 0, st>>>(A, lda, M, K, v, T, out, alpha, beta); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+cudaError_t gpk_launch_gemv_t(const double* A, int lda, int M, int K, const double* v, int T, double* out, double alpha,
+                              cudaStream_t st) {
+  if (M <= 0) return cudaSuccess;
+  dim3 grid((K + 127) / 128, (M + 511) / 512);
+  gpk_gemv_t_kernel<<<grid, 128, 0, st>>>(A, lda, M, K, v, T, out, alpha); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+cudaError_t gpk_launch_fix_diag(double* A, int lda, int n, int n_valid, double add, double pad, cudaStream_t st) {
+  gpk_fix_diag_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, n_valid, add, pad); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+cudaError_t gpk_launch_logdiag(const double* A, int lda, int n, double* s, cudaStream_t st) {
+  gpk_logdiag_kernel<<<1, 256, 0, st>>>(A, lda, n, s); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
