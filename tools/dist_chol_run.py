@@ -1,6 +1,6 @@
 """torchrun driver for the distributed GP factorisation (BASELINE config 5).
   python -m torch.distributed.run --nnodes=1 --nproc-per-node P --master-addr 127.0.0.1 --master-port 29511 \
-      tools/dist_chol_run.py --n 200000 --nb 2048 [--check]
+      tools/dist_chol_run.py --size 200000 --block 2048 [--check]
 Rank 0 prints one JSON line and appends it to gpurun_out/dist_chol.jsonl."""
 import argparse, json, os, sys, time
 import numpy as np, torch, torch.distributed as dist
@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from unmanned_aerial_vehicles_b200.dist_chol import DistGP
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, default=200000); ap.add_argument("--nb", type=int, default=2048)
+ap.add_argument("--size", dest="n", type=int, default=200000); ap.add_argument("--block", dest="nb", type=int, default=2048)
 ap.add_argument("--check", action="store_true")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
