@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpk.so")
+LIB_PATH = os.environ.get("GPK_LIB", os.path.join(_HERE, "libgpk.so"))
 
 # every symbol include/gpk.h declares (tests check the .so exports exactly these)
 SYMBOLS = (

@@ -20,6 +20,7 @@ cudaError_t gpk_launch_potrf_inv(double*, int, double*, double*, int, int, int*,
 cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
 cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
+cudaError_t gpk_launch_dmma16816_probe(int, int, double*, cudaStream_t);
 cudaError_t gpk_launch_gemv_n(const double*, int, int, int, const double*, int, double*, double, double, cudaStream_t);
 cudaError_t gpk_launch_gemv_t(const double*, int, int, int, const double*, int, double*, double, cudaStream_t);
 cudaError_t gpk_launch_fix_diag(double*, int, int, int, double, double, cudaStream_t);
@@ -157,6 +158,11 @@ int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* 
   return 0;
 }
 int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream) {
+  if (blocks < 0) {  // negative block count selects the m16n8k16 shape: 8 warps x 8 accumulators x 4096 flops
+    GPK_CHECK(gpk_launch_dmma16816_probe(-blocks, iters, sink_d, (cudaStream_t)stream));
+    if (flops_h) *flops_h = (double)(-blocks) * 8.0 * 8.0 * 4096.0 * (double)iters;
+    return 0;
+  }
   GPK_CHECK(gpk_launch_dmma_probe(blocks, iters, sink_d, (cudaStream_t)stream));
   // 256 threads = 8 warps, 16 independent m8n8k4 accumulators per warp, 512 flops each
   if (flops_h) *flops_h = (double)blocks * 8.0 * 16.0 * 512.0 * (double)iters;

@@ -5,9 +5,17 @@
 // CTA tile 128x128, k-tile 16, 3-stage cp.async pipeline, 8 warps (2 x 4), warp tile 64 x 32.
 #include "gpk_common.cuh"
 
+#ifndef KT
 #define KT 16                 // k-tile
-#define LDSM 20               // padded smem row stride in doubles (conflict-free 8x4 fragment reads)
+#endif
+#define LDSM (KT + 4)         // padded smem row stride in doubles (== 4 mod 16: conflict-free 8x4 fragment reads)
+#ifndef GEMM_WR
+#define GEMM_WR 2
+#define GEMM_WC 4
+#endif
+#ifndef STAGES
 #define STAGES 3
+#endif
 #define GEMM_THREADS 256
 #define GEMM_SMEM_BYTES_TS(TS) (STAGES * 2 * (TS) * LDSM * 8)
 #define GPK_PROF_CAP 16384
@@ -26,20 +34,6 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
-
-template <int TS, int NTHR>
-__device__ __forceinline__ void load_stage(double* sA, double* sB, const double* __restrict__ A, int lda,
-                                           const double* __restrict__ B, int ldb, int m0, int n0, int k0,
-                                           int tid) {
-  // TS rows x 16 doubles = TS*8 16-byte chunks per operand
-#pragma unroll
-  for (int i = 0; i < TS * 8 / NTHR; ++i) {
-    int chunk = tid + i * NTHR;
-    int r = chunk >> 3, c = (chunk & 7) * 2;
-    cp_async16(sA + r * LDSM + c, A + (size_t)(m0 + r) * lda + k0 + c);
-    cp_async16(sB + r * LDSM + c, B + (size_t)(n0 + r) * ldb + k0 + c);
-  }
 }
 
 // TS: CTA tile edge (128 / 64 / 32); WR x WC warps, warp tile (TS/WR) x (TS/WC)
@@ -75,26 +69,35 @@ __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt
 #pragma unroll
     for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
+  // per-thread incremental global pointers: chunk i of this thread is row (tid/CPR + i*NTHR/CPR), 16-byte column tid%CPR
+  constexpr int CPR = KT / 2, NCH = TS * CPR / NTHR, RSTEP = NTHR / CPR;
+  const int lr = tid / CPR, lc = (tid % CPR) * 2;
+  const double* pA = g.A + (size_t)(m0 + lr) * g.lda + kb + lc;
+  const double* pB = g.B + (size_t)(n0 + lr) * g.ldb + kb + lc;
+  const size_t stepA = (size_t)RSTEP * g.lda, stepB = (size_t)RSTEP * g.ldb;
+  const int soff = lr * LDSM + lc;
+  auto prefetch = [&](int slot) {
+    double* sA = smem + slot * STAGE_DOUBLES + soff;
+    double* sB = sA + TS * LDSM;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      cp_async16(sA + i * RSTEP * LDSM, pA + i * stepA);
+      cp_async16(sB + i * RSTEP * LDSM, pB + i * stepB);
+    }
+    pA += KT; pB += KT;
+  };
   // prologue
 #pragma unroll
   for (int s = 0; s < STAGES - 1; ++s) {
-    if (s < nk) {
-      double* sA = smem + s * STAGE_DOUBLES;
-      load_stage<TS, NTHR>(sA, sA + TS * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + s * KT, tid);
-    }
+    if (s < nk) prefetch(s);
     cp_async_commit();
   }
+  // The two warps that share an SM sub-partition (warp, warp + 4) issue their prefetch at different points of the
+  // k-tile, so one of them always keeps the DMMA pipe fed while the other does address math / LDGSTS issue.
+  const int pf_kk = ((warp >> 2) & 1) ? (KT / 2) : 0;
   for (int kt = 0; kt < nk; ++kt) {
     cp_async_wait<STAGES - 2>();
     __syncthreads();
-    {  // prefetch tile kt + STAGES - 1 into the slot consumed at iteration kt - 1
-      int nxt = kt + STAGES - 1;
-      if (nxt < nk) {
-        double* sA = smem + (nxt % STAGES) * STAGE_DOUBLES;
-        load_stage<TS, NTHR>(sA, sA + TS * LDSM, g.A, g.lda, g.B, g.ldb, m0, n0, kb + nxt * KT, tid);
-      }
-      cp_async_commit();
-    }
     const double* sA = smem + (kt % STAGES) * STAGE_DOUBLES;
     const double* sB = sA + TS * LDSM;
 #pragma unroll
@@ -108,6 +111,11 @@ __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt
       for (int i = 0; i < MT; ++i)
 #pragma unroll
         for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+      if (kk == pf_kk) {  // prefetch tile kt + STAGES - 1 into the slot consumed at iteration kt - 1
+        const int nxt = kt + STAGES - 1;
+        if (nxt < nk) prefetch(nxt % STAGES);
+        cp_async_commit();
+      }
     }
   }
   cp_async_wait<0>();
@@ -171,7 +179,7 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
     if (!g_ev0[g_gpk_prof.n]) { cudaEventCreate(&g_ev0[g_gpk_prof.n]); cudaEventCreate(&g_ev1[g_gpk_prof.n]); }
     cudaEventRecord(g_ev0[g_gpk_prof.n], st);
   }
-  cudaError_t le = ts == 128 ? launch_ts<128, 2, 4>(g, st) : ts == 64 ? launch_ts<64, 2, 2>(g, st) : launch_ts<32, 2, 2>(g, st);
+  cudaError_t le = ts == 128 ? launch_ts<128, GEMM_WR, GEMM_WC>(g, st) : ts == 64 ? launch_ts<64, 2, 2>(g, st) : launch_ts<32, 2, 2>(g, st);
   if (le != cudaSuccess) return le;
   GPK_LAUNCHED();
   if (prof) {
@@ -264,4 +272,38 @@ int gpk_profile_launch_info(int i, double* seconds, double* flops, int* mnk) {
   cudaEventElapsedTime(&ms, g_ev0[i], g_ev1[i]);
   *seconds = ms * 1e-3; *flops = g_lflops[i]; mnk[0] = g_shape[i][0]; mnk[1] = g_shape[i][1]; mnk[2] = g_shape[i][2];
   return 0;
+}
+
+// ---- probe of the sm_90+ m16n8k16 f64 shape (does sm_100a run it at the m8n8k4 rate or better?) ------------
+__device__ __forceinline__ void dmma16816(double (&c)[4], const double (&a)[8], const double (&b)[4]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7,%8,%9,%10,%11}, "
+      "{%12,%13,%14,%15}, {%0,%1,%2,%3};\n"
+      : "+d"(c[0]), "+d"(c[1]), "+d"(c[2]), "+d"(c[3])
+      : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(a[4]), "d"(a[5]), "d"(a[6]), "d"(a[7]), "d"(b[0]), "d"(b[1]),
+        "d"(b[2]), "d"(b[3]));
+}
+__global__ void __launch_bounds__(256) gpk_dmma16816_probe_kernel(int iters, double* sink) {
+  double acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+  double a[8], b[4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a[i] = 1.0 + 1e-9 * (threadIdx.x + i);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) b[i] = 1.0 - 1e-9 * (threadIdx.x + i);
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dmma16816(acc[i], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += acc[i][0] + acc[i][1] + acc[i][2] + acc[i][3];
+  if (s == 12345.678) sink[0] = s;
+}
+cudaError_t gpk_launch_dmma16816_probe(int blocks, int iters, double* sink, cudaStream_t st) {
+  gpk_dmma16816_probe_kernel<<<blocks, 256, 0, st>>>(iters, sink);
+  return cudaGetLastError();
 }
