@@ -23,67 +23,77 @@
 //                                            c = j :          S[i][j]  = -l_ij / d
 //   i.e. forward elimination applied to [A | I] at once, so S ends as L^-1 while column j of L is streamed out.
 // info: first failing global pivot index + 1 (LAPACK convention), 0 if none.
-__global__ void __launch_bounds__(256, 1)
+#define LEAF_THREADS 512
+#define LEAF_RA 4   // rows per thread: 128 / 32
+// publish helpers: the owner index is uniform across the CTA, so a switch replaces 8-way register selects
+#define LEAF_COL_CASE(B)                                                            \
+  case B:                                                                           \
+    _Pragma("unroll") for (int a = 0; a < LEAF_RA; ++a) {                           \
+      const int i = ty + 32 * a;                                                    \
+      if (i > j) buf[p][i] = S[a][B];                                               \
+      else if (i == j) { piv[p] = S[a][B]; buf[p][j] = 1.0; }                       \
+      S[a][B] = 0.0;  /* column j restarts as the M-part: S[i][j] = 0 - l_ij/d */   \
+    }                                                                               \
+    break;
+#define LEAF_ROW_CASE(AA)                                                           \
+  case AA:                                                                          \
+    _Pragma("unroll") for (int b = 0; b < 8; ++b) {                                 \
+      const int c = tx + 16 * b;                                                    \
+      if (c < j) buf[p][c] = S[AA][b];                                              \
+    }                                                                               \
+    break;
+
+__global__ void __launch_bounds__(LEAF_THREADS, 1)
 gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ Mlow, double* __restrict__ Mup,
                           int ldm, int off, int* __restrict__ info) {
-  __shared__ double colbuf[2][GPK_TILE], rowbuf[2][GPK_TILE];
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  // buf[p][x]: x < j  -> raw M[j][x] (row j);  x == j -> 1;  x > j -> raw A[x][j] (column j).  piv[p] = A[j][j].
+  __shared__ double buf[2][GPK_TILE], piv[2];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;   // 32 x 16 threads; rows ty+32a, cols tx+16b
   double* Ab = A + (size_t)off * lda + off;
-  double S[8][8];
+  double S[LEAF_RA][8];
 #pragma unroll
-  for (int a = 0; a < 8; ++a)
+  for (int a = 0; a < LEAF_RA; ++a)
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
-      const int i = ty + 16 * a, c = tx + 16 * b;
+      const int i = ty + 32 * a, c = tx + 16 * b;
       S[a][b] = (c <= i) ? Ab[(size_t)i * lda + c] : 0.0;
     }
   for (int j = 0; j < GPK_TILE; ++j) {
-    const int p = j & 1, bj = j >> 4, tj = j & 15;
-    if (tx == tj) {
-#pragma unroll
-      for (int a = 0; a < 8; ++a) {
-        double v = 0.0;
-#pragma unroll
-        for (int b = 0; b < 8; ++b) if (b == bj) v = S[a][b];
-        const int i = ty + 16 * a;
-        if (i >= j) colbuf[p][i] = v;
-      }
+    const int p = j & 1;
+    if (ty == (j & 31)) {          // row j first (reads S[j][c], c < j), then column j (which zeroes S[.][j])
+      switch (j >> 5) { LEAF_ROW_CASE(0) LEAF_ROW_CASE(1) LEAF_ROW_CASE(2) LEAF_ROW_CASE(3) }
     }
-    if (ty == tj) {
-#pragma unroll
-      for (int b = 0; b < 8; ++b) {
-        double v = 0.0;
-#pragma unroll
-        for (int a = 0; a < 8; ++a) if (a == bj) v = S[a][b];
-        const int c = tx + 16 * b;
-        if (c < j) rowbuf[p][c] = v;
+    if (tx == (j & 15)) {
+      switch (j >> 4) {
+        LEAF_COL_CASE(0) LEAF_COL_CASE(1) LEAF_COL_CASE(2) LEAF_COL_CASE(3)
+        LEAF_COL_CASE(4) LEAF_COL_CASE(5) LEAF_COL_CASE(6) LEAF_COL_CASE(7)
       }
     }
     __syncthreads();
-    double d = colbuf[p][j];
+    double d = piv[p];
     if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
       if (tid == 0) { int want = off + j + 1; int old = atomicCAS(info, 0, want); if (old != 0 && old > want) atomicMin(info, want); }
       d = __longlong_as_double(0x7ff8000000000000LL);
     }
-    const double ljj = sqrt(d), dinv = 1.0 / ljj;
+    // 1/sqrt(d) with one Newton step each on sqrt and reciprocal (no FP64 division on the critical path)
+    double dinv = rsqrt(d);
+    double ljj = d * dinv;
+    ljj = fma(0.5 * dinv, fma(-ljj, ljj, d), ljj);
+    dinv = fma(dinv, fma(-ljj, dinv, 1.0), dinv);
     double v[8];
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const int c = tx + 16 * b;
-      v[b] = ((c < j) ? rowbuf[p][c] : colbuf[p][c]) * dinv;   // c == j handled below
-    }
+    for (int b = 0; b < 8; ++b) v[b] = buf[p][tx + 16 * b] * dinv;
 #pragma unroll
-    for (int a = 0; a < 8; ++a) {
-      const int i = ty + 16 * a;
+    for (int a = 0; a < LEAF_RA; ++a) {
+      const int i = ty + 32 * a;
       if (i > j) {
-        const double li = colbuf[p][i] * dinv;
+        const double li = buf[p][i] * dinv;
+        // whole row at once: c > j is the Cholesky update, c < j the inverse update, c == j gives -l_ij/d;
+        // entries above the diagonal (c > i) hold finite garbage that nothing reads
 #pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          const int c = tx + 16 * b;
-          if (c <= i) S[a][b] = (c == j) ? (-li * dinv) : (S[a][b] - li * v[b]);
-        }
-        if (tx == tj) Ab[(size_t)i * lda + j] = li;          // column j of L
-      } else if (i == j) {                                  // row j of M becomes final
+        for (int b = 0; b < 8; ++b) S[a][b] = fma(-li, v[b], S[a][b]);
+        if (tx == (j & 15)) Ab[(size_t)i * lda + j] = li;          // column j of L
+      } else if (i == j) {                                         // row j of M becomes final
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
           const int c = tx + 16 * b;
@@ -96,10 +106,10 @@ gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ 
   double* Ml = Mlow + (size_t)off * ldm + off;
   double* Mu = Mup + (size_t)off * ldm + off;
 #pragma unroll
-  for (int a = 0; a < 8; ++a)
+  for (int a = 0; a < LEAF_RA; ++a)
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
-      const int i = ty + 16 * a, c = tx + 16 * b;
+      const int i = ty + 32 * a, c = tx + 16 * b;
       const double m = (c <= i) ? S[a][b] : 0.0;
       Ml[(size_t)i * ldm + c] = m;
       Mu[(size_t)c * ldm + i] = m;
@@ -111,7 +121,7 @@ struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info;
 static void chol_rec(CholCtx& c, int off, int n) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
-    gpk_leaf_potrf_inv_kernel<<<1, 256, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info); GPK_LAUNCHED();
+    gpk_leaf_potrf_inv_kernel<<<1, LEAF_THREADS, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info); GPK_LAUNCHED();
     c.err = cudaGetLastError();
     return;
   }
