@@ -1,5 +1,5 @@
-"""Distributed (1-D block-column-cyclic) Cholesky: host logic on CPU with a NumPy/gloo ops object (world sizes 1
-and 2), and the real CUDA ops on one GPU against the single-GPU engine."""
+"""Distributed 2-D block-cyclic Cholesky with look-ahead: host logic on CPU with a NumPy/gloo ops object (world
+sizes 1, 2 and 4; grids 1x1, 1x2, 2x1, 2x2, 1x4), and the real CUDA ops on one GPU against the single-GPU engine."""
 import os
 import socket
 import sys
@@ -15,9 +15,37 @@ class NumpyOps:
 
     def __init__(self, dist=None):
         self.dist = dist
+        self.groups = {"world": None, "row": None, "col": None}
+        self.log = []
 
     def rank_world(self):
         return (self.dist.get_rank(), self.dist.get_world_size()) if self.dist else (0, 1)
+
+    def make_grid(self, Pr, Pc):
+        rank, P = self.rank_world()
+        assert Pr * Pc == P
+        pr, pc = rank // Pc, rank % Pc
+        if P > 1:
+            for r in range(Pr):
+                g = self.dist.new_group([r * Pc + c for c in range(Pc)]) if Pc > 1 else None
+                if r == pr: self.groups["row"] = g
+            for c in range(Pc):
+                g = self.dist.new_group([r * Pc + c for r in range(Pr)]) if Pr > 1 else None
+                if c == pc: self.groups["col"] = g
+        return pr, pc
+
+    def info_slots(self, n): self.infos = np.zeros(max(n, 1), dtype=np.int32)
+    def read_infos(self): return self.infos
+
+    import contextlib as _cl
+
+    @_cl.contextmanager
+    def side(self):
+        self.log.append("side+")
+        yield
+        self.log.append("side-")
+
+    def join_side(self): self.log.append("join")
 
     def zeros(self, r, c): return np.zeros((r, c))
     def empty(self, r, c): return np.full((r, c), np.nan)
@@ -37,15 +65,16 @@ class NumpyOps:
         for i in range(n):
             A[i, i] = A[i, i] + add if i < n_valid else pad
 
-    def potrf_inv(self, A, Ml, Mu, NB):
+    def potrf_inv(self, A, Ml, Mu, NB, slot):
         try:
             L = np.linalg.cholesky(np.tril(A) + np.tril(A, -1).T)
         except np.linalg.LinAlgError:
-            return 1
+            self.infos[slot] = 1
+            A[...] = np.nan; Ml[...] = np.nan; Mu[...] = np.nan
+            return
         A[...] = L
         Ml[...] = np.linalg.inv(L)
         Mu[...] = Ml.T
-        return 0
 
     def gemm_nt(self, A, B, Cm, M, N, K, alpha, acc, b_tri=0):
         Bm = np.tril(B[:N, :K]) if b_tri == 1 else B[:N, :K]
@@ -68,9 +97,11 @@ class NumpyOps:
         import torch
         return torch.from_numpy(a)
 
-    def bcast(self, buf, src):
-        if self.dist:
-            t = self._t(np.ascontiguousarray(buf)); self.dist.broadcast(t, src=src); buf[...] = t.numpy()
+    def bcast(self, buf, src, kind="world"):
+        if not self.dist or (kind != "world" and self.groups[kind] is None):
+            return
+        t = self._t(np.ascontiguousarray(buf)); self.dist.broadcast(t, src=src, group=self.groups[kind])
+        buf[...] = t.numpy()
 
     def allreduce_sum(self, buf):
         if self.dist:
@@ -98,45 +129,96 @@ def _check(g, X, Y, ls, c, noise, jit):
 
 
 def test_single_rank_numpy_ops():
-    from unmanned_aerial_vehicles_b200.dist_chol import DistGP
+    from unmanned_aerial_vehicles_b200.dist_chol import DistGP, default_grid
+    assert [default_grid(p) for p in (1, 2, 4, 6, 8)] == [(1, 1), (1, 2), (2, 2), (2, 3), (2, 4)]
     X, Y, ls, c, noise, jit = _problem()
     g = DistGP(X, Y, jit, NB=128, ops=NumpyOps())
-    assert g.nb == 3 and g.NP == 384 and g.owned == [0, 1, 2]
+    assert g.nb == 3 and g.NP == 384 and g.owned == [0, 1, 2] and g.diag == [0, 1, 2]
     assert g.factor(1.0 / ls, c, noise) == 0
+    # look-ahead: the broadcasts of panel k+1 are issued on the side stream, joined before panel k+1 is used
+    assert g.ops.log[:4] == ["side+", "side-", "join", "side+"] and g.ops.log[-1] == "join"
     g.solve()
     _check(g, X, Y, ls, c, noise, jit)
+    g2 = DistGP(X, Y, jit, NB=128, ops=NumpyOps(), lookahead=False)
+    assert g2.factor(1.0 / ls, c, noise) == 0 and "side+" not in g2.ops.log
+    g2.solve()
+    _check(g2, X, Y, ls, c, noise, jit)
     bad = DistGP(np.zeros((200, 4)), Y[:200], 0.0, NB=128, ops=NumpyOps())
-    assert bad.factor(1.0 / ls, 1.0, 0.0) != 0
+    assert bad.factor(1.0 / ls, 1.0, 0.0) == 1          # info = k*NB + block info (the NumPy double reports 1)
+    with pytest.raises(ValueError):
+        DistGP(X, Y, jit, NB=128, ops=NumpyOps(), grid=(2, 1))
 
 
-def _worker(rank, world, port, q):
+def test_tile_ownership_maps():
+    """every lower tile has exactly one owner and the local stacking matches (i % Pr, j % Pc)"""
+    from unmanned_aerial_vehicles_b200.dist_chol import DistGP
+
+    class FakeOps(NumpyOps):
+        def __init__(self, rank, P): super().__init__(); self.r, self.P = rank, P
+        def rank_world(self): return self.r, self.P
+        def make_grid(self, Pr, Pc): return self.r // Pc, self.r % Pc
+
+    X, Y, *_ = _problem(n=1100)
+    for Pr, Pc in [(2, 4), (4, 2), (1, 8), (2, 2), (3, 2)]:
+        seen = {}
+        for r in range(Pr * Pc):
+            g = DistGP(X, Y, 1e-6, NB=128, ops=FakeOps(r, Pr * Pc), grid=(Pr, Pc))
+            assert sorted(g.colpos.values()) == list(range(g.nlc))
+            for j in g.my_cols:
+                rows = [i for i in g.my_rows if i >= j]
+                assert g.cols[j].shape == (len(rows) * 128, 128)
+                assert g.lfirst(j) == len([i for i in g.my_rows if i < j])
+                for i in rows:
+                    assert (i, j) not in seen and g.owner(i, j) == r
+                    seen[(i, j)] = r
+        assert len(seen) == g.nb * (g.nb + 1) // 2
+
+
+def _worker(rank, world, port, q, grid, n):
     sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from test_dist_chol import NumpyOps, _check, _problem
     from unmanned_aerial_vehicles_b200.dist_chol import DistGP
-    X, Y, ls, c, noise, jit = _problem(n=600)
-    g = DistGP(X, Y, jit, NB=128, ops=NumpyOps(dist))
+    X, Y, ls, c, noise, jit = _problem(n=n)
+    g = DistGP(X, Y, jit, NB=128, ops=NumpyOps(dist), grid=grid)
     info = g.factor(1.0 / ls, c, noise)
     g.solve()
     _check(g, X, Y, ls, c, noise, jit)
-    q.put((rank, info, g.owned, g.lml()))
+    bad = DistGP(np.zeros((300, 4)), Y[:300], 0.0, NB=128, ops=NumpyOps(dist), grid=grid)
+    q.put((rank, info, g.owned, g.lml(), bad.factor(1.0 / ls, 1.0, 0.0)))
     dist.barrier(); dist.destroy_process_group()
 
 
-def test_two_ranks_gloo():
+def _run(world, grid, n):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, grid, n)) for r in range(world)]
     [p.start() for p in procs]
-    outs = sorted(q.get(timeout=300) for _ in range(2))
+    outs = sorted(q.get(timeout=300) for _ in range(world))
     [p.join(60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
-    assert outs[0][1] == 0 and outs[0][2] == [0, 2, 4] and outs[1][2] == [1, 3]
-    assert outs[0][3] == outs[1][3]
+    assert all(o[1] == 0 for o in outs) and all(o[3] == outs[0][3] for o in outs)
+    assert all(o[4] == 1 for o in outs)                 # non-PD: same info on every rank
+    return outs
+
+
+def test_two_ranks_gloo_1x2():
+    outs = _run(2, (1, 2), 600)
+    assert outs[0][2] == [0, 2, 4] and outs[1][2] == [1, 3]
+
+
+def test_two_ranks_gloo_2x1():
+    outs = _run(2, (2, 1), 600)
+    assert outs[0][2] == [0, 1, 2, 3, 4] == outs[1][2]
+
+
+@pytest.mark.parametrize("grid,n", [((2, 2), 1000), ((1, 4), 700), ((4, 1), 700)])
+def test_four_ranks_gloo(grid, n):
+    _run(4, grid, n)
 
 
 @pytest.mark.gpu

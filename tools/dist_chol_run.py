@@ -1,6 +1,6 @@
 """torchrun driver for the distributed GP factorisation (BASELINE config 5).
   python -m torch.distributed.run --nnodes=1 --nproc-per-node P --master-addr 127.0.0.1 --master-port 29511 \
-      tools/dist_chol_run.py --size 200000 --block 2048 [--check]
+      tools/dist_chol_run.py --size 200000 --block 2048 [--grid 2x4] [--no-lookahead] [--check]
 Rank 0 prints one JSON line and appends it to gpurun_out/dist_chol.jsonl."""
 import argparse, json, os, sys, time
 import numpy as np, torch, torch.distributed as dist
@@ -10,6 +10,8 @@ from unmanned_aerial_vehicles_b200.dist_chol import DistGP
 ap = argparse.ArgumentParser()
 ap.add_argument("--size", dest="n", type=int, default=200000); ap.add_argument("--block", dest="nb", type=int, default=2048)
 ap.add_argument("--check", action="store_true")
+ap.add_argument("--grid", default="", help="PrxPc, e.g. 2x4 (default: most square)")
+ap.add_argument("--no-lookahead", action="store_true")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
 torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
@@ -21,7 +23,8 @@ X = rng.standard_normal((a.n, D)); w = rng.standard_normal((D, T)) / 3
 Y = np.sin(X @ w) + 0.1 * rng.standard_normal((a.n, T))
 ls, noise, jit = np.ones(D), 0.01, 1e-6
 t0 = time.perf_counter()
-g = DistGP(X, Y, jit, NB=a.nb)
+grid = tuple(int(v) for v in a.grid.split("x")) if a.grid else None
+g = DistGP(X, Y, jit, NB=a.nb, grid=grid, lookahead=not a.no_lookahead)
 torch.cuda.synchronize()
 if world > 1: dist.barrier()
 t1 = time.perf_counter()
@@ -36,7 +39,7 @@ fl = torch.tensor([g.gemm_flops], dtype=torch.float64, device="cuda")
 mem = torch.tensor([torch.cuda.max_memory_allocated() / 2 ** 30], dtype=torch.float64, device="cuda")
 if world > 1:
     dist.all_reduce(fl); dist.all_reduce(mem, op=dist.ReduceOp.MAX)
-out = {"what": "dist_chol", "n": a.n, "nb": a.nb, "n_gpus": world, "T": T, "info": info, "alloc_s": t1 - t0,
+out = {"what": "dist_chol", "n": a.n, "nb": a.nb, "n_gpus": world, "grid": f"{g.Pr}x{g.Pc}", "lookahead": g.lookahead, "T": T, "info": info, "alloc_s": t1 - t0,
        "assemble_factor_s": t2 - t1, "solve_lml_s": t3 - t2, "lml": lml, "potrf_alg_tflops": (a.n ** 3 / 3) / (t2 - t1) / 1e12,
        "executed_gemm_tflops": float(fl[0]) / (t2 - t1) / 1e12, "max_mem_gib_per_gpu": float(mem[0]),
        "local_gib": g.local_bytes() / 2 ** 30}

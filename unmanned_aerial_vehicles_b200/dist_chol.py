@@ -1,17 +1,24 @@
 """Exact GP factorisation for training sets too large for one GPU (BASELINE config 5: N=200k, 320 GB Gram).
 
-1-D block-column-cyclic right-looking Cholesky over the ranks of a torch.distributed group (NCCL over
-NVLink/NVSwitch on GPUs).  Block column j (width NB, rows j*NB..NP) lives on rank j % P; only the lower
-trapezoid is stored (N^2/2/P doubles per rank: 20 GB at N=200k, P=8).  K is generated in place from the
-replicated X (14 MB) so the Gram matrix is never communicated.  Per panel k:
+2-D block-cyclic right-looking Cholesky with one-panel look-ahead over a Pr x Pc process grid of a
+torch.distributed group (NCCL over NVLink/NVSwitch on GPUs).  Tile (i, j) (NB x NB, i >= j) lives on grid
+position (i % Pr, j % Pc); rank r sits at (r // Pc, r % Pc).  Only the lower trapezoid is stored, one tensor per
+owned block column holding that column's owned row tiles stacked (N^2/2/P doubles per rank: 20 GB at N=200k,
+P=8).  K is generated in place from the replicated X (14 MB) so the Gram matrix is never communicated.
 
-    owner:  L_kk, L_kk^-1 = potrf_inv(A_kk)  (the single-GPU recursive kernel);  L_{>k,k} = A_{>k,k} L_kk^-T
-    all  :  ncclBroadcast of the factored panel ((NP - k NB) x NB doubles)
-    all  :  A_{>=j, j} -= L_{>=j,k} L_{j,k}^T   for every owned block column j > k   (DMMA NT GEMMs, K = NB)
+Per panel k (process column pck = k % Pc):
 
-Total broadcast volume is N^2/2 doubles = 160 GB at N=200k, i.e. ~0.25 s at the measured 700 GB/s against
-~11 s of FP64 tensor work per rank, so a 2-D grid (smaller volume, more complex) is not needed on NVSwitch.
-alpha = K^-1 y by distributed forward/back substitution (one tiny all-reduce / broadcast per panel), then
+    diag owner        L_kk, L_kk^-1 = potrf_inv(A_kk)          (the single-GPU recursive kernel)
+    process column    ncclBroadcast of L_kk^-1 down the column group;  L_ik = A_ik L_kk^-T for the owned rows i > k
+    process rows      ncclBroadcast of the owned L_ik along each row group (root: the rank in column pck)
+    process columns   transposed exchange: rank (j % Pr, pc) broadcasts L_jk (j % Pc == pc) down column group pc
+    all               A_ij -= L_ik L_jk^T for every owned tile i >= j > k   (DMMA NT GEMMs, K = NB)
+
+Look-ahead: block column k+1 is updated first, panel k+1 is factored, and its two broadcasts are issued on a side
+stream into the second panel buffer while the main stream finishes the trailing update of panel k.
+Received volume per rank is 8 (N^2/2)(1/Pr + 1/Pc) bytes (120 GB on 2x4 at N=200k, 160 GB on 1x8).  A 1 x P grid
+degenerates to the 1-D block-column-cyclic layout (no column exchange).
+alpha = K^-1 y by distributed forward/back substitution (one small all-reduce + broadcast per panel), then
 lml = -1/2 y.alpha - T sum log L_ii - T N/2 log 2 pi  (sklearn _gpr.py:601-617).
 
 The numerical work goes through an `ops` object: `CudaOps` (libgpk.so + NCCL) is the product; the tests inject
@@ -19,11 +26,20 @@ a NumPy/gloo implementation to exercise the distributed logic on CPU.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 
 import numpy as np
 
 from . import _lib
+
+
+def default_grid(P):
+    """most square Pr x Pc with Pr <= Pc (8 -> 2x4, 4 -> 2x2, 2 -> 1x2)"""
+    pr = int(np.floor(np.sqrt(P)))
+    while P % pr:
+        pr -= 1
+    return pr, P // pr
 
 
 class CudaOps:
@@ -39,6 +55,8 @@ class CudaOps:
         self.lib = _lib.load()
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.info = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.groups = {"world": group, "row": None, "col": None}
+        self.side_stream = torch.cuda.Stream(device=self.dev)
 
     def _st(self):
         return C.c_void_p(self.t.cuda.current_stream().cuda_stream)
@@ -50,6 +68,23 @@ class CudaOps:
     def rank_world(self):
         d = self.dist
         return (d.get_rank(self.group), d.get_world_size(self.group)) if d.is_initialized() else (0, 1)
+
+    def make_grid(self, Pr, Pc):
+        """row / column sub-communicators of the Pr x Pc grid (every rank creates every group, same order)"""
+        rank, P = self.rank_world()
+        assert Pr * Pc == P
+        pr, pc = rank // Pc, rank % Pc
+        if P > 1:
+            for r in range(Pr):
+                g = self.dist.new_group([r * Pc + c for c in range(Pc)]) if Pc > 1 else None
+                if r == pr:
+                    self.groups["row"] = g
+            for c in range(Pc):
+                g = self.dist.new_group([r * Pc + c for r in range(Pr)]) if Pr > 1 else None
+                if c == pc:
+                    self.groups["col"] = g
+        self.grid = (Pr, Pc)
+        return pr, pc
 
     def zeros(self, rows, cols):
         return self.t.zeros((rows, cols), dtype=self.t.float64, device=self.dev)
@@ -63,6 +98,9 @@ class CudaOps:
     def to_host(self, a):
         return a.cpu().numpy()
 
+    def info_slots(self, n):
+        self.infos = self.t.zeros(max(n, 1), dtype=self.t.int32, device=self.dev)
+
     def gram_block(self, Xq, mq, Xc, nc, D, inv_ls, c, out, MP, NB):
         """out (MP x NB) = c*rbf(Xq[:mq], Xc[:nc]) (zero padded)"""
         _lib.check(self.lib.gpk_cross_gram(self._p(Xq), mq, self._p(Xc), nc, D, _lib.darr(inv_ls), c, self._p(out),
@@ -71,10 +109,13 @@ class CudaOps:
     def fix_diag(self, A, n, n_valid, add, pad):
         _lib.check(self.lib.gpk_fix_diag(self._p(A), A.stride(0), n, n_valid, add, pad, self._st()), "gpk_fix_diag")
 
-    def potrf_inv(self, A, Ml, Mu, NB):
-        _lib.check(self.lib.gpk_potrf_inv(self._p(A), self._p(Ml), self._p(Mu), NB, self._p(self.info), self._st()),
-                   "gpk_potrf_inv")
-        return int(self.info.cpu()[0])
+    def potrf_inv(self, A, Ml, Mu, NB, slot):
+        """info (LAPACK convention, relative to this block) is left in device slot `slot`: no host sync here"""
+        _lib.check(self.lib.gpk_potrf_inv(self._p(A), self._p(Ml), self._p(Mu), NB, self._p(self.infos[slot:]),
+                                          self._st()), "gpk_potrf_inv")
+
+    def read_infos(self):
+        return self.infos.cpu().numpy()
 
     def gemm_nt(self, A, B, Cm, M, N, K, alpha, acc, b_tri=0):
         _lib.check(self.lib.gpk_gemm_nt(self._p(A), A.stride(0), self._p(B), B.stride(0), self._p(Cm), Cm.stride(0),
@@ -98,141 +139,261 @@ class CudaOps:
     def logdiag(self, A, n, acc):
         _lib.check(self.lib.gpk_logdiag(self._p(A), A.stride(0), n, self._p(acc), self._st()), "gpk_logdiag")
 
-    def bcast(self, buf, src):
-        if self.dist.is_initialized() and self.rank_world()[1] > 1:
-            self.dist.broadcast(buf, src=src, group=self.group)
+    def _multi(self):
+        return self.dist.is_initialized() and self.rank_world()[1] > 1
+
+    def bcast(self, buf, src, kind="world"):
+        """src is the rank within the world group; kind selects world / grid-row / grid-column communicator"""
+        if not self._multi():
+            return
+        g = self.groups[kind]
+        if kind != "world" and g is None:
+            return                      # group of one
+        self.dist.broadcast(buf, src=src, group=g)
 
     def allreduce_sum(self, buf):
-        if self.dist.is_initialized() and self.rank_world()[1] > 1:
+        if self._multi():
             self.dist.all_reduce(buf, group=self.group)
 
+    @contextlib.contextmanager
+    def side(self):
+        """enqueue on the side stream, ordered after everything issued so far on the main stream"""
+        main = self.t.cuda.current_stream()
+        self.side_stream.wait_stream(main)
+        with self.t.cuda.stream(self.side_stream):
+            yield
+
+    def join_side(self):
+        self.t.cuda.current_stream().wait_stream(self.side_stream)
+
+    def sync(self):
+        self.t.cuda.synchronize()
+
     def allreduce_max_int(self, v):
-        if self.dist.is_initialized() and self.rank_world()[1] > 1:
+        if self._multi():
             tt = self.t.tensor([v], dtype=self.t.int64, device=self.dev)
             self.dist.all_reduce(tt, op=self.dist.ReduceOp.MAX, group=self.group)
             return int(tt[0])
         return v
 
-    def sync(self):
-        self.t.cuda.synchronize()
-
 
 class DistGP:
     """Distributed exact GP: factor K(theta) + alpha*I, solve for alpha_, evaluate the LML."""
 
-    def __init__(self, X, y2d, jitter, NB=2048, ops=None):
+    def __init__(self, X, y2d, jitter, NB=2048, ops=None, grid=None, lookahead=True):
         self.ops = ops if ops is not None else CudaOps()
         self.rank, self.P = self.ops.rank_world()
+        self.Pr, self.Pc = grid if grid is not None else default_grid(self.P)
+        if self.Pr * self.Pc != self.P:
+            raise ValueError(f"grid {self.Pr}x{self.Pc} does not match world size {self.P}")
+        self.pr, self.pc = self.ops.make_grid(self.Pr, self.Pc)
         X = np.ascontiguousarray(X, dtype=np.float64)
         y2d = np.ascontiguousarray(y2d, dtype=np.float64)
         self.N, self.D = X.shape
         self.T = y2d.shape[1]
         assert NB % 128 == 0
         self.NB = NB
-        self.nb = (self.N + NB - 1) // NB
-        self.NP = self.nb * NB
+        self.nb = nb = (self.N + NB - 1) // NB
+        self.NP = nb * NB
         self.jitter = float(jitter)
-        o = self.ops
+        self.lookahead = bool(lookahead)
+        o, Pr, Pc, pr, pc = self.ops, self.Pr, self.Pc, self.pr, self.pc
+        self.my_rows = [i for i in range(nb) if i % Pr == pr]
+        self.my_cols = [j for j in range(nb) if j % Pc == pc]
+        self.owned = self.my_cols                      # block columns this rank holds tiles of
+        self.nlr, self.nlc = len(self.my_rows), len(self.my_cols)
+        # training inputs: replicated (column operand) and this rank's row tiles stacked (row operand)
+        Xpad = np.zeros((self.NP, self.D))
+        Xpad[: self.N] = X
         self.X_d = o.from_host(X)
+        self.Xrow_d = o.from_host(Xpad.reshape(nb, NB, self.D)[self.my_rows].reshape(-1, self.D))
+        self.nvalid_loc = sum(max(0, min(NB, self.N - i * NB)) for i in self.my_rows)
         ypad = np.zeros((self.NP, self.T))
         ypad[: self.N] = y2d
         self.y_d = o.from_host(ypad)
-        self.owned = [j for j in range(self.nb) if j % self.P == self.rank]
-        self.cols = {j: o.empty(self.NP - j * NB, NB) for j in self.owned}       # lower trapezoid only
-        self.Ml = {j: o.empty(NB, NB) for j in self.owned}                        # L_jj^-1
-        self.Mu = {j: o.empty(NB, NB) for j in self.owned}                        # L_jj^-T
-        self.buf = o.empty(self.NP, NB)                                           # panel broadcast buffer
+        # lower trapezoid: per owned block column, the owned row tiles i >= j stacked
+        self.cols = {j: o.empty((self.nlr - self.lfirst(j)) * NB, NB) for j in self.my_cols}
+        self.diag = [k for k in self.my_cols if k % Pr == pr]
+        self.Ml = {k: o.empty(NB, NB) for k in self.diag}                         # L_kk^-1
+        self.Mu = {k: o.empty(NB, NB) for k in self.diag}                         # L_kk^-T
+        self.mlbuf = o.empty(NB, NB)
+        # panel buffers (double-buffered for the look-ahead): L_ik for my rows, L_jk for my columns.
+        # Lcol is ordered by the grid row that roots each piece of the transposed exchange.
+        self.Lrow = [o.empty(max(self.nlr, 1) * NB, NB) for _ in range(2)]
+        self.Lcol = [o.empty(max(self.nlc, 1) * NB, NB) for _ in range(2)]
+        self.seg = [[j for j in self.my_cols if j % Pr == rp] for rp in range(Pr)]
+        self.colpos = {}
+        for rp in range(Pr):
+            for j in self.seg[rp]:
+                self.colpos[j] = len(self.colpos)
+        o.info_slots(nb)
         self.gemm_flops = 0.0
         self.factored = False
 
-    def owner(self, j):
-        return j % self.P
+    # -- index helpers --------------------------------------------------------------------------------
+    def lfirst(self, m):
+        """number of this rank's row tiles with global index < m (= local index of the first owned row >= m)"""
+        if m <= self.pr:
+            return 0
+        return min(self.nlr, (m - self.pr + self.Pr - 1) // self.Pr)
+
+    def owner(self, i, j=None):
+        """world rank of tile (i, j); owner(k) is the diagonal tile (k, k)"""
+        j = i if j is None else j
+        return (i % self.Pr) * self.Pc + (j % self.Pc)
 
     def local_bytes(self):
-        return 8 * (sum((self.NP - j * self.NB) * self.NB for j in self.owned) + 2 * len(self.owned) * self.NB ** 2
-                    + self.NP * self.NB)
+        NB = self.NB
+        tiles = sum(self.nlr - self.lfirst(j) for j in self.my_cols) + 2 * len(self.diag) + 1
+        tiles += 2 * max(self.nlr, 1) + 2 * max(self.nlc, 1)
+        return 8 * tiles * NB * NB
 
-    # -- K generated in place ---------------------------------------------------------------------
+    # -- K generated in place -------------------------------------------------------------------------
     def assemble(self, inv_ls, c, noise):
         o, NB, N = self.ops, self.NB, self.N
-        for j in self.owned:
-            r0 = j * NB
-            rows = self.NP - r0
-            mq = max(0, N - r0)
-            nc = max(0, min(NB, N - r0))
-            o.gram_block(self.X_d[r0:], mq, self.X_d[r0:], nc, self.D, inv_ls, c, self.cols[j], rows, NB)
-            # diagonal: (c + noise) + jitter on real rows (gram gives c there), identity in the padding
-            o.fix_diag(self.cols[j], NB, nc, noise, 1.0)          # (c + noise), padding -> 1
-            o.fix_diag(self.cols[j], nc, nc, self.jitter, 1.0)    # ... + alpha  (_gpr.py:589)
+        for j in self.my_cols:
+            l0 = self.lfirst(j)
+            rows = (self.nlr - l0) * NB
+            if rows == 0:
+                continue
+            mq = max(0, self.nvalid_loc - l0 * NB)
+            nc = max(0, min(NB, N - j * NB))
+            o.gram_block(self.Xrow_d[l0 * NB:], mq, self.X_d[j * NB:], nc, self.D, inv_ls, c, self.cols[j], rows, NB)
+            if j % self.Pr == self.pr:
+                # diagonal tile: (c + noise) + jitter on real rows (gram gives c there), identity in the padding
+                o.fix_diag(self.cols[j], NB, nc, noise, 1.0)          # (c + noise), padding -> 1
+                o.fix_diag(self.cols[j], nc, nc, self.jitter, 1.0)    # ... + alpha  (_gpr.py:589)
 
-    # -- right-looking factorisation ----------------------------------------------------------------
+    # -- right-looking factorisation with one-panel look-ahead ----------------------------------------
+    def _panel_factor(self, k, b):
+        """process column k % Pc: factor the diagonal tile, form L_ik = A_ik L_kk^-T into Lrow[b] (and in place)"""
+        o, NB = self.ops, self.NB
+        if self.pc != k % self.Pc:
+            return
+        Ck = self.cols[k]
+        own_diag = self.pr == k % self.Pr
+        if own_diag:
+            o.potrf_inv(Ck[:NB], self.Ml[k], self.Mu[k], NB, k)
+            o.copy(self.Ml[k], self.mlbuf)
+        o.bcast(self.mlbuf, self.owner(k), "col")
+        off = NB if own_diag else 0
+        rows = Ck.shape[0] - off
+        if rows > 0:
+            l0 = self.lfirst(k + 1)
+            dst = self.Lrow[b][l0 * NB: l0 * NB + rows]
+            o.gemm_nt(Ck[off:], self.mlbuf, dst, rows, NB, NB, 1.0, 0, b_tri=1)
+            o.copy(dst, Ck[off:])
+            self.gemm_flops += rows * float(NB) * NB
+
+    def _panel_bcast(self, k, b):
+        """row broadcast of L_ik, then the transposed exchange down the process columns (fills Lrow[b], Lcol[b])"""
+        o, NB, Pr, Pc = self.ops, self.NB, self.Pr, self.Pc
+        l0 = self.lfirst(k + 1)
+        if self.nlr - l0 > 0:
+            o.bcast(self.Lrow[b][l0 * NB: self.nlr * NB], self.pr * Pc + k % Pc, "row")
+        row3 = self.Lrow[b].reshape(-1, NB, NB)
+        col3 = self.Lcol[b].reshape(-1, NB, NB)
+        for rp in range(Pr):
+            js = [j for j in self.seg[rp] if j > k]
+            if not js:
+                continue
+            c0, c1 = self.colpos[js[0]], self.colpos[js[-1]] + 1
+            if self.pr == rp:
+                step = (js[1] - js[0]) // Pr if len(js) > 1 else 1
+                o.copy(row3[js[0] // Pr: js[-1] // Pr + 1: step], col3[c0:c1])
+            o.bcast(self.Lcol[b][c0 * NB: c1 * NB], rp * Pc + self.pc, "col")
+
+    def _update(self, k, b, js):
+        """A[i >= j, j] -= L[i >= j, k] L[j, k]^T for the owned block columns in js"""
+        o, NB = self.ops, self.NB
+        for j in js:
+            Cj = self.cols[j]
+            M = Cj.shape[0]
+            if M == 0:
+                continue
+            l0 = self.lfirst(j)
+            p = self.colpos[j]
+            o.gemm_nt(self.Lrow[b][l0 * NB:], self.Lcol[b][p * NB: (p + 1) * NB], Cj, M, NB, NB, -1.0, 1)
+            self.gemm_flops += 2.0 * M * NB * NB
+
     def factor(self, inv_ls, c, noise):
         o, NB, nb = self.ops, self.NB, self.nb
+        side = o.side if self.lookahead else contextlib.nullcontext
         self.assemble(inv_ls, c, noise)
-        info = 0
+        self._panel_factor(0, 0)
+        with side():
+            self._panel_bcast(0, 0)
         for k in range(nb):
-            rows = self.NP - k * NB
-            buf = self.buf[:rows]
-            if self.owner(k) == self.rank:
-                Ck = self.cols[k]
-                bi = o.potrf_inv(Ck[:NB], self.Ml[k], self.Mu[k], NB)
-                if bi and not info:
-                    info = k * NB + bi
-                o.copy(Ck[:NB], buf[:NB])
-                if rows > NB:
-                    o.gemm_nt(Ck[NB:], self.Ml[k], buf[NB:], rows - NB, NB, NB, 1.0, 0, b_tri=1)
-                    o.copy(buf[NB:], Ck[NB:])
-                    self.gemm_flops += (rows - NB) * float(NB) * NB
-            o.bcast(buf, self.owner(k))
-            for j in self.owned:
-                if j <= k:
-                    continue
-                off = (j - k) * NB
-                # A[j.., j] -= L[j.., k] L[j, k]^T
-                o.gemm_nt(buf[off:], buf[off:off + NB], self.cols[j], rows - off, NB, NB, -1.0, 1)
-                self.gemm_flops += 2.0 * (rows - off) * NB * NB
-        info = o.allreduce_max_int(info)
+            b = k % 2
+            o.join_side()                      # panel k has arrived in Lrow[b] / Lcol[b]
+            if k + 1 < nb:
+                if self.pc == (k + 1) % self.Pc:
+                    self._update(k, b, [k + 1])
+                self._panel_factor(k + 1, 1 - b)
+                with side():                   # overlaps the rest of the trailing update below
+                    self._panel_bcast(k + 1, 1 - b)
+            self._update(k, b, [j for j in self.my_cols if j > k + 1])
+        o.join_side()
+        infos = o.read_infos()
+        bad = [k * NB + int(infos[k]) for k in self.diag if infos[k] != 0]
+        BIG = 1 << 40
+        r = o.allreduce_max_int(BIG - min(bad) if bad else 0)
+        info = BIG - r if r > 0 else 0
         self.factored = info == 0
         return info
 
     # -- alpha = K^-1 y, log-det, lml -----------------------------------------------------------------
     def solve(self):
         assert self.factored
-        o, NB, nb, T = self.ops, self.NB, self.nb, self.T
-        z = o.zeros(self.NP, T)            # this rank's partial sums  sum_k L[:,k] u_k  over owned k
+        o, NB, nb, T, Pr, Pc = self.ops, self.NB, self.nb, self.T, self.Pr, self.Pc
+        nl = max(self.nlr, 1) * NB
+        z = o.zeros(nl, T)                 # sum_k L_ik u_k over this rank's tiles, my rows (local order)
         u = o.zeros(self.NP, T)
         t = o.empty(NB, T)
         for k in range(nb):                # forward: L u = y
             blk = slice(k * NB, (k + 1) * NB)
-            o.copy(z[blk], t)
+            if self.pr == k % Pr:
+                lk = k // Pr
+                o.copy(z[lk * NB: (lk + 1) * NB], t)
+            else:
+                o.zero(t)
             o.allreduce_sum(t)
             if self.owner(k) == self.rank:
                 rhs = self.y_d[blk] - t
                 o.trimv(self.Ml[k], rhs, u[blk], upper=False)
-                if k + 1 < nb:
-                    o.gemv(self.cols[k][NB:], u[blk], z[(k + 1) * NB:], 1.0, 1.0, transpose=False)
             o.bcast(u[blk], self.owner(k))
+            if self.pc == k % Pc:
+                off = NB if self.pr == k % Pr else 0
+                if self.cols[k].shape[0] - off > 0:
+                    o.gemv(self.cols[k][off:], u[blk], z[self.lfirst(k + 1) * NB: self.nlr * NB], 1.0, 1.0,
+                           transpose=False)
         alpha = o.zeros(self.NP, T)
+        a_loc = o.zeros(nl, T)             # alpha restricted to my rows (local order)
         s = o.zeros(NB, T)
         for k in range(nb - 1, -1, -1):    # backward: L^T alpha = u
             blk = slice(k * NB, (k + 1) * NB)
+            o.zero(s)
+            if self.pc == k % Pc:
+                off = NB if self.pr == k % Pr else 0
+                if self.cols[k].shape[0] - off > 0:
+                    o.gemv(self.cols[k][off:], a_loc[self.lfirst(k + 1) * NB: self.nlr * NB], s, 1.0, 0.0,
+                           transpose=True)
+            o.allreduce_sum(s)
             if self.owner(k) == self.rank:
-                if k + 1 < nb:
-                    o.zero(s)
-                    o.gemv(self.cols[k][NB:], alpha[(k + 1) * NB:], s, 1.0, 0.0, transpose=True)
-                    rhs = u[blk] - s
-                else:
-                    rhs = u[blk] + 0.0
+                rhs = u[blk] - s
                 o.trimv(self.Mu[k], rhs, alpha[blk], upper=True)
             o.bcast(alpha[blk], self.owner(k))
+            if self.pr == k % Pr:
+                lk = k // Pr
+                o.copy(alpha[blk], a_loc[lk * NB: (lk + 1) * NB])
         self.alpha_d, self.u_d = alpha, u
         return alpha
 
     def lml(self):
         o = self.ops
         acc = o.zeros(1, 1)
-        for j in self.owned:
-            o.logdiag(self.cols[j], self.NB, acc)
+        for k in self.diag:
+            o.logdiag(self.cols[k], self.NB, acc)
         o.allreduce_sum(acc)
         logdet = float(o.to_host(acc)[0, 0])
         y = o.to_host(self.y_d)[: self.N]
