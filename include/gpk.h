@@ -101,6 +101,9 @@ int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
 unsigned long long gpk_launch_count(void);
 int gpk_profile_begin(void);
 int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h);
+/* SM-clock cycles thread 0 of the most recent Cholesky leaf spent per phase (8 slots: load, diagonal potrf,
+ * panel, trailing update, diagonal inverses, off-diagonal inverse blocks, store, unused); synchronises. */
+int gpk_leaf_phase_cycles(long long* out_h);
 /* after gpk_profile_end: duration, executed flops and (M,N,K) of the i-th recorded GEMM launch */
 int gpk_profile_launch(int i, double* seconds_h, double* flops_h, int* mnk_h);
 

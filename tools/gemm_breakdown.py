@@ -27,14 +27,23 @@ for i in range(nl.value):
 for k in sorted(agg):
     n, s, f = agg[k]
     print(f"dim<={k:6d} launches {n:4d} time {s*1e3:8.2f} ms  flops {f:.3e}  {f/s/1e12:6.2f} TF/s")
+cyc = (C.c_longlong * 8)()
+lib.gpk_leaf_phase_cycles(cyc)
+print("last leaf of the step, phase cycles [load,P1,P2,P3,I1,I2,store]:", list(cyc)[:7], "total", sum(cyc))
 # leaf latency: potrf_inv on a single 128x128 block, averaged over 200 back-to-back launches
 A = torch.eye(128, dtype=torch.float64, device="cuda") * 2 + 0.01
 Ml = torch.empty_like(A); Mu = torch.empty_like(A); info = torch.zeros(1, dtype=torch.int32, device="cuda")
 P = lambda t: C.c_void_p(t.data_ptr()); st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 A0 = A.clone()
+# (A is restored before every launch: refactoring the factor in place drifts into denormals and a slow rsqrt path)
 for rep in range(2):
-    e0.record()
-    for _ in range(200):
-        lib.gpk_potrf_inv(P(A), P(Ml), P(Mu), 128, P(info), st)
-    e1.record(); torch.cuda.synchronize()
-print("leaf potrf_inv(128) us per launch (incl. memset):", e0.elapsed_time(e1) * 1e3 / 200)
+    tot = 0.0
+    for _ in range(100):
+        A.copy_(A0)
+        e0.record(); lib.gpk_potrf_inv(P(A), P(Ml), P(Mu), 128, P(info), st); e1.record(); torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+print("leaf potrf_inv(128) us per launch (incl. memset, event overhead):", tot * 1e3 / 100)
+cyc = (C.c_longlong * 8)()
+lib.gpk_leaf_phase_cycles(cyc)
+names = ["load", "P1 diag potrf", "P2 panel", "P3 trailing", "I1 diag inverse", "I2 off-diag inverse", "store", "-"]
+print("leaf phase cycles:", {n: int(v) for n, v in zip(names, cyc)}, "total", sum(cyc))

@@ -16,7 +16,7 @@ SYMBOLS = (
     "gpk_abi_version", "gpk_pad", "gpk_lml_out_len", "gpk_grad_workspace_doubles", "gpk_gram",
     "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
     "gpk_predict_mean", "gpk_predict_std", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
-    "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
+    "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_leaf_phase_cycles", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
 )
 
 
@@ -58,6 +58,7 @@ def _declare(lib):
     lib.gpk_trimv.argtypes = [_p, _i, _p, _p, _i, _i, _p]
     lib.gpk_fix_diag.argtypes = [_p, _i, _i, _i, _d, _d, _p]
     lib.gpk_logdiag.argtypes = [_p, _i, _i, _p, _p]
+    lib.gpk_leaf_phase_cycles.argtypes = [_p]
     lib.gpk_launch_count.restype = C.c_ulonglong
     lib.gpk_profile_launch.argtypes = [_i, _dp, _dp, C.POINTER(C.c_int)]
     lib.gpk_profile_end.argtypes = [_dp, _dp, C.POINTER(C.c_int)]

@@ -30,6 +30,7 @@ unsigned long long g_gpk_launches = 0;
 GpkProfile g_gpk_prof = {0, 0, 0.0};
 double gpk_profile_collect();
 int gpk_profile_launch_info(int, double*, double*, int*);
+cudaError_t gpk_leaf_cycles(long long* out_h);
 
 static int make_params(GpkKernelParams& p, int D, const double* inv_ls_h, double c, double noise, double jitter) {
   if (D < 1 || D > GPK_MAXD) return -1;
@@ -190,6 +191,12 @@ int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream) 
   return 0;
 }
 unsigned long long gpk_launch_count(void) { return g_gpk_launches; }
+int gpk_leaf_phase_cycles(long long* out_h) {
+  if (!out_h) return -1;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1000;
+  GPK_CHECK(gpk_leaf_cycles(out_h));
+  return 0;
+}
 int gpk_profile_launch(int i, double* seconds_h, double* flops_h, int* mnk_h) { return gpk_profile_launch_info(i, seconds_h, flops_h, mnk_h); }
 int gpk_profile_begin(void) { g_gpk_prof.enabled = 1; g_gpk_prof.n = 0; g_gpk_prof.flops = 0.0; return 0; }
 int gpk_profile_end(double* gemm_seconds_h, double* gemm_flops_h, int* n_launches_h) {

@@ -12,67 +12,56 @@
 //   rec(11);  L21 = A21 * M11^T;  A22 -= L21 L21^T;  rec(22);  M21 = -M22 * L21 * M11.
 #include "gpk_common.cuh"
 
-#define LEAF_SMEM_BYTES 0
-
-// One CTA factors a 128x128 diagonal block and inverts the factor in the same sweep.
-// The block lives in REGISTERS: 16x16 threads, thread (ty,tx) owns S[ty+16a][tx+16b], a,b < 8 (2-D cyclic).
-// Step j (one __syncthreads each, buffers double-buffered):
-//   column j (raw) and row j (raw) are published to shared memory; d = sqrt(pivot);
-//   for every row i > j and column c <= i:   c > j : A-part   S[i][c] -= l_ij * l_cj
-//                                            c < j : M-part   S[i][c] -= l_ij * M[j][c]
-//                                            c = j :          S[i][j]  = -l_ij / d
-//   i.e. forward elimination applied to [A | I] at once, so S ends as L^-1 while column j of L is streamed out.
+// ---------------------------------------------------------------------------------------------------------
+// Leaf: one CTA factors a 128x128 diagonal block and inverts the factor (L, L^-1, L^-T out).
+// v4: blocked at 32 inside shared memory (the block never leaves the SM between load and store):
+//   for kb = 0..3:  P1  warp 0 factors the 32x32 diagonal block in registers (lane = row; the column of
+//                       multipliers is broadcast with shuffles, no barrier inside the 32 column steps)
+//                   P2  one thread per row below: forward substitution x L_kk^T = a  (panel, in place)
+//                   P3  all threads: trailing update A22 -= P P^T on 16x16-cyclic register tiles
+//   I1  warps 0..3 invert the four diagonal blocks (lane = column, axpy form)
+//   I2  off-diagonal blocks of L^-1 by block forward substitution, level by level:
+//       M_ij = -M_ii (sum_{j<=k<i} L_ik M_kj)
+// Shared memory: S (128 x 129) holds A -> L in its lower triangle and the off-diagonal blocks of L^-1
+// TRANSPOSED in its upper triangle; diagonal blocks of L^-1 live in Mkk.  Row stride 129 makes both row and
+// column walks bank-conflict free for 64-bit accesses.
 // info: first failing global pivot index + 1 (LAPACK convention), 0 if none.
-#define LEAF_THREADS 512
-#define LEAF_RA 4   // rows per thread: 128 / 32
-// publish helpers: the owner index is uniform across the CTA, so a switch replaces 8-way register selects
-#define LEAF_COL_CASE(B)                                                            \
-  case B:                                                                           \
-    _Pragma("unroll") for (int a = 0; a < LEAF_RA; ++a) {                           \
-      const int i = ty + 32 * a;                                                    \
-      if (i > j) buf[p][i] = S[a][B];                                               \
-      else if (i == j) { piv[p] = S[a][B]; buf[p][j] = 1.0; }                       \
-      S[a][B] = 0.0;  /* column j restarts as the M-part: S[i][j] = 0 - l_ij/d */   \
-    }                                                                               \
-    break;
-#define LEAF_ROW_CASE(AA)                                                           \
-  case AA:                                                                          \
-    _Pragma("unroll") for (int b = 0; b < 8; ++b) {                                 \
-      const int c = tx + 16 * b;                                                    \
-      if (c < j) buf[p][c] = S[AA][b];                                              \
-    }                                                                               \
-    break;
+#define LEAF_THREADS 256
+#define LF_LD 129
+struct LeafSmem {
+  double S[GPK_TILE * LF_LD];
+  double Mkk[4][32 * 33];
+  double LT[32 * 32];      // LT[c][c2] = L_kk[c2][c] (transposed copy of the current diagonal block)
+  double W[3][32 * 33];
+  double dinv[GPK_TILE];   // 1 / L_ii
+  double col[2][48];       // P1: raw pivot column, double-buffered (reads run up to 15 entries past 32)
+};
+#define LEAF_SMEM_BYTES ((int)sizeof(LeafSmem))
 
-__global__ void __launch_bounds__(LEAF_THREADS, 1)
-gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ Mlow, double* __restrict__ Mup,
-                          int ldm, int off, int* __restrict__ info) {
-  // buf[p][x]: x < j  -> raw M[j][x] (row j);  x == j -> 1;  x > j -> raw A[x][j] (column j).  piv[p] = A[j][j].
-  __shared__ double buf[2][GPK_TILE], piv[2];
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;   // 32 x 16 threads; rows ty+32a, cols tx+16b
-  double* Ab = A + (size_t)off * lda + off;
-  double S[LEAF_RA][8];
-#pragma unroll
-  for (int a = 0; a < LEAF_RA; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const int i = ty + 32 * a, c = tx + 16 * b;
-      S[a][b] = (c <= i) ? Ab[(size_t)i * lda + c] : 0.0;
-    }
-  for (int j = 0; j < GPK_TILE; ++j) {
-    const int p = j & 1;
-    if (ty == (j & 31)) {          // row j first (reads S[j][c], c < j), then column j (which zeroes S[.][j])
-      switch (j >> 5) { LEAF_ROW_CASE(0) LEAF_ROW_CASE(1) LEAF_ROW_CASE(2) LEAF_ROW_CASE(3) }
-    }
-    if (tx == (j & 15)) {
-      switch (j >> 4) {
-        LEAF_COL_CASE(0) LEAF_COL_CASE(1) LEAF_COL_CASE(2) LEAF_COL_CASE(3)
-        LEAF_COL_CASE(4) LEAF_COL_CASE(5) LEAF_COL_CASE(6) LEAF_COL_CASE(7)
-      }
-    }
-    __syncthreads();
-    double d = piv[p];
+__device__ __forceinline__ void leaf_record(int* info, int want) {
+  int old = atomicCAS(info, 0, want);
+  if (old != 0 && old > want) atomicMin(info, want);
+}
+
+// P1: warp-synchronous potrf of the 32x32 block at (k0,k0); lane i owns row i in registers.
+// The code is kept SMALL (rolled loops): a fully unrolled sweep is ~3500 straight-line instructions executed
+// once by one warp and runs at instruction-fetch speed (measured 38k cycles per block).  Registers rotate so
+// that the active column is always r[0] (the FMA writes r[c-1]), which keeps the indexing static inside a
+// rolled loop.  Each step publishes the raw column through a double-buffered shared vector, so one
+// __syncwarp per column is the only synchronisation; the update uses r_c -= (a_i a_c) / d.
+template <int W>
+__device__ __forceinline__ void leaf_potrf_chunk(double (&r)[32], LeafSmem& sm, int k0, int jbase, int lane, int off,
+                                                 int* info) {
+#pragma unroll 1
+  for (int s = 0; s < 8; ++s) {
+    const int j = jbase + s;
+    double* buf = sm.col[j & 1];
+    const double raw = r[0];
+    buf[lane] = raw;
+    __syncwarp();
+    double d = buf[j];
     if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
-      if (tid == 0) { int want = off + j + 1; int old = atomicCAS(info, 0, want); if (old != 0 && old > want) atomicMin(info, want); }
+      if (lane == 0) leaf_record(info, off + k0 + j + 1);
       d = __longlong_as_double(0x7ff8000000000000LL);
     }
     // 1/sqrt(d) with one Newton step each on sqrt and reciprocal (no FP64 division on the critical path)
@@ -80,40 +69,239 @@ gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ 
     double ljj = d * dinv;
     ljj = fma(0.5 * dinv, fma(-ljj, ljj, d), ljj);
     dinv = fma(dinv, fma(-ljj, dinv, 1.0), dinv);
-    double v[8];
+    const double li = (lane > j) ? raw * dinv : (lane == j ? ljj : 0.0);   // finished rows contribute nothing
+    sm.S[(k0 + lane) * LF_LD + k0 + j] = li;
+    sm.LT[j * 32 + lane] = li;
+    if (lane == j) sm.dinv[k0 + j] = dinv;
+    const double sc = -li * dinv;
+    const double* bj = buf + j;
 #pragma unroll
-    for (int b = 0; b < 8; ++b) v[b] = buf[p][tx + 16 * b] * dinv;
+    for (int c = 1; c < W; ++c) r[c - 1] = fma(sc, bj[c], r[c]);
+  }
+}
+__device__ __forceinline__ void leaf_diag_potrf(LeafSmem& sm, int k0, int lane, int off, int* info) {
+  double r[32];
+  const double* row = sm.S + (k0 + lane) * LF_LD + k0;
 #pragma unroll
-    for (int a = 0; a < LEAF_RA; ++a) {
-      const int i = ty + 32 * a;
-      if (i > j) {
-        const double li = buf[p][i] * dinv;
-        // whole row at once: c > j is the Cholesky update, c < j the inverse update, c == j gives -l_ij/d;
-        // entries above the diagonal (c > i) hold finite garbage that nothing reads
+  for (int c = 0; c < 32; ++c) r[c] = row[c];
+  leaf_potrf_chunk<32>(r, sm, k0, 0, lane, off, info);
+  leaf_potrf_chunk<24>(r, sm, k0, 8, lane, off, info);
+  leaf_potrf_chunk<16>(r, sm, k0, 16, lane, off, info);
+  leaf_potrf_chunk<8>(r, sm, k0, 24, lane, off, info);
+}
+
+// P2: rows below the diagonal block, one thread per row: x L_kk^T = a by forward substitution (axpy form)
+__device__ __forceinline__ void leaf_panel_row(LeafSmem& sm, int k0, int i) {
+  double a[32];
+  double* row = sm.S + i * LF_LD + k0;
 #pragma unroll
-        for (int b = 0; b < 8; ++b) S[a][b] = fma(-li, v[b], S[a][b]);
-        if (tx == (j & 15)) Ab[(size_t)i * lda + j] = li;          // column j of L
-      } else if (i == j) {                                         // row j of M becomes final
+  for (int c = 0; c < 32; ++c) a[c] = row[c];
 #pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          const int c = tx + 16 * b;
-          if (c < j) S[a][b] *= dinv;
-          else if (c == j) { S[a][b] = dinv; Ab[(size_t)j * lda + j] = ljj; }
+  for (int c = 0; c < 32; ++c) {
+    const double x = a[c] * sm.dinv[k0 + c];
+    a[c] = x;
+#pragma unroll
+    for (int c2 = c + 1; c2 < 32; ++c2) a[c2] = fma(-x, sm.LT[c * 32 + c2], a[c2]);
+  }
+#pragma unroll
+  for (int c = 0; c < 32; ++c) row[c] = a[c];
+}
+
+// P3: A[i][c] -= sum_k P[i][k] P[c][k] over the trailing rows/cols (NRB 32-blocks), lower 16x16 sub-tiles only.
+// Thread (ty,tx) of a 16x16 grid owns rows base+ty+16a, cols base+tx+16b.
+template <int NRB>
+__device__ __forceinline__ void leaf_trailing(LeafSmem& sm, int k0, int base, int tx, int ty) {
+  constexpr int NA = 2 * NRB;
+  double acc[NA][NA];
+#pragma unroll
+  for (int a = 0; a < NA; ++a)
+#pragma unroll
+    for (int b = 0; b < NA; ++b) acc[a][b] = 0.0;
+  const double* pr = sm.S + (base + ty) * LF_LD + k0;
+  const double* pc = sm.S + (base + tx) * LF_LD + k0;
+#pragma unroll 4
+  for (int k = 0; k < 32; ++k) {
+    double rv[NA], cv[NA];
+#pragma unroll
+    for (int a = 0; a < NA; ++a) { rv[a] = pr[a * 16 * LF_LD + k]; cv[a] = pc[a * 16 * LF_LD + k]; }
+#pragma unroll
+    for (int a = 0; a < NA; ++a)
+#pragma unroll
+      for (int b = 0; b <= a; ++b) acc[a][b] = fma(rv[a], cv[b], acc[a][b]);
+  }
+#pragma unroll
+  for (int a = 0; a < NA; ++a)
+#pragma unroll
+    for (int b = 0; b <= a; ++b) {
+      const int i = base + ty + 16 * a, c = base + tx + 16 * b;
+      if (c <= i) sm.S[i * LF_LD + c] -= acc[a][b];
+    }
+}
+
+// I1: inverse of the 32x32 lower-triangular diagonal block b; lane c computes column c (zeros above the diagonal)
+__device__ __forceinline__ void leaf_diag_inverse(LeafSmem& sm, int b, int lane) {
+  const int k0 = 32 * b;
+  double t[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) t[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    const double mk = t[k] * sm.dinv[k0 + k];
+    t[k] = mk;
+    const double* lcol = sm.S + (k0 + k) * LF_LD + k0 + k;   // L[k0+i][k0+k] = lcol[(i-k)*LF_LD]
+#pragma unroll
+    for (int i = k + 1; i < 32; ++i) t[i] = fma(-lcol[(i - k) * LF_LD], mk, t[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < 32; ++i) sm.Mkk[b][i * 33 + lane] = t[i];
+}
+
+// cycle stamps of the last leaf launch (thread 0): load, P1, P2, P3 (summed over kb), I1, I2, store
+__device__ long long g_leaf_cycles[8];
+#define LEAF_STAMP(slot) do { if (tid == 0) { long long t__ = clock64(); cyc[slot] += t__ - tprev; tprev = t__; } } while (0)
+
+// M[k][c] for k >= c in different 32-blocks is stored transposed in the upper triangle: S[c][k]
+__global__ void __launch_bounds__(LEAF_THREADS, 1)
+gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ Mlow, double* __restrict__ Mup,
+                          int ldm, int off, int* __restrict__ info) {
+  extern __shared__ __align__(16) unsigned char leaf_smem_raw[];
+  LeafSmem& sm = *reinterpret_cast<LeafSmem*>(leaf_smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tx = tid & 15, ty = tid >> 4;
+  double* Ab = A + (size_t)off * lda + off;
+  long long cyc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+  for (int idx = tid; idx < GPK_TILE * GPK_TILE; idx += LEAF_THREADS) {
+    const int i = idx >> 7, c = idx & 127;
+    sm.S[i * LF_LD + c] = (c <= i) ? Ab[(size_t)i * lda + c] : 0.0;
+  }
+  if (tid < 96) sm.col[0][tid] = 0.0;
+  __syncthreads();
+  LEAF_STAMP(0);
+  // ---- factorisation ------------------------------------------------------------------------------
+#pragma unroll 1
+  for (int kb = 0; kb < 4; ++kb) {
+    const int k0 = 32 * kb, base = k0 + 32;
+    if (warp == 0) leaf_diag_potrf(sm, k0, lane, off, info);
+    __syncthreads();
+    LEAF_STAMP(1);
+    if (kb == 3) break;
+    if (tid < GPK_TILE - base) leaf_panel_row(sm, k0, base + tid);
+    __syncthreads();
+    LEAF_STAMP(2);
+    if (kb == 0) leaf_trailing<3>(sm, k0, base, tx, ty);
+    else if (kb == 1) leaf_trailing<2>(sm, k0, base, tx, ty);
+    else leaf_trailing<1>(sm, k0, base, tx, ty);
+    __syncthreads();
+    LEAF_STAMP(3);
+  }
+  // ---- inverse --------------------------------------------------------------------------------------
+  if (warp < 4) leaf_diag_inverse(sm, warp, lane);
+  __syncthreads();
+  LEAF_STAMP(4);
+  // level d handles the 4-d blocks (ib = jb + d); 64 threads per block, each a 4x4 register tile
+  // (rows ty4+8a, cols tx4+8b): 8 shared loads per 16 FMAs
+  {
+    const int bi = tid >> 6, t64 = tid & 63, tx4 = t64 & 7, ty4 = t64 >> 3;
+#pragma unroll 1
+    for (int d = 1; d < 4; ++d) {
+      const bool active = bi < 4 - d;
+      const int ib = bi + d, jb = bi, i0 = 32 * ib, j0 = 32 * jb;
+      if (active) {
+        // W[r][c] = sum_{k=j0}^{i0-1} L[i0+r][k] M[k][j0+c]
+        double acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        const double* lrow = sm.S + (i0 + ty4) * LF_LD;
+        const double* mk = sm.Mkk[jb] + tx4;
+#pragma unroll 2
+        for (int k = 0; k < 32; ++k) {                               // k inside block jb: diagonal block of M
+          double lv[4], mv[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) { lv[a] = lrow[a * 8 * LF_LD + j0 + k]; mv[a] = mk[k * 33 + 8 * a]; }
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fma(lv[a], mv[b], acc[a][b]);
         }
+        const double* mt = sm.S + (j0 + tx4) * LF_LD;
+#pragma unroll 2
+        for (int k = j0 + 32; k < i0; ++k) {                         // later blocks: transposed storage
+          double lv[4], mv[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) { lv[a] = lrow[a * 8 * LF_LD + k]; mv[a] = mt[a * 8 * LF_LD + k]; }
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fma(lv[a], mv[b], acc[a][b]);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) sm.W[bi][(ty4 + 8 * a) * 33 + tx4 + 8 * b] = acc[a][b];
       }
+      __syncthreads();
+      if (active) {
+        // M_ij[r][c] = -sum_{k<=r} M_ii[r][k] W[k][c]  -> stored transposed at S[j0+c][i0+r]
+        double acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        const double* mi = sm.Mkk[ib] + ty4 * 33;
+        const double* wk = sm.W[bi] + tx4;
+#pragma unroll 2
+        for (int k = 0; k < 32; ++k) {
+          double lv[4], mv[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) { lv[a] = mi[a * 8 * 33 + k]; mv[a] = wk[k * 33 + 8 * a]; }
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fma(lv[a], mv[b], acc[a][b]);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) sm.S[(j0 + tx4 + 8 * b) * LF_LD + i0 + ty4 + 8 * a] = -acc[a][b];
+      }
+      __syncthreads();
     }
   }
+  LEAF_STAMP(5);
+  // ---- store L (lower), L^-1 (lower, zeros above), L^-T (upper, zeros below) -------------------------
   double* Ml = Mlow + (size_t)off * ldm + off;
   double* Mu = Mup + (size_t)off * ldm + off;
+  for (int idx = tid; idx < GPK_TILE * GPK_TILE; idx += LEAF_THREADS) {
+    const int i = idx >> 7, c = idx & 127;       // row i, column c of the output matrices
+    if (c <= i) Ab[(size_t)i * lda + c] = sm.S[i * LF_LD + c];
+    // Mlow[i][c] = M[i][c]
+    double m = 0.0;
+    if ((c >> 5) == (i >> 5)) m = sm.Mkk[i >> 5][(i & 31) * 33 + (c & 31)];
+    else if (c < i) m = sm.S[c * LF_LD + i];
+    Ml[(size_t)i * ldm + c] = m;
+    // Mup[i][c] = M[c][i]
+    double u = 0.0;
+    if ((c >> 5) == (i >> 5)) u = sm.Mkk[i >> 5][(c & 31) * 33 + (i & 31)];
+    else if (c > i) u = sm.S[i * LF_LD + c];
+    Mu[(size_t)i * ldm + c] = u;
+  }
+  LEAF_STAMP(6);
+  if (tid == 0) {
 #pragma unroll
-  for (int a = 0; a < LEAF_RA; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const int i = ty + 32 * a, c = tx + 16 * b;
-      const double m = (c <= i) ? S[a][b] : 0.0;
-      Ml[(size_t)i * ldm + c] = m;
-      Mu[(size_t)c * ldm + i] = m;
-    }
+    for (int q = 0; q < 8; ++q) g_leaf_cycles[q] = cyc[q];
+  }
+}
+
+cudaError_t gpk_leaf_cycles(long long* out_h) {
+  return cudaMemcpyFromSymbol(out_h, g_leaf_cycles, sizeof(long long) * 8);
+}
+
+static cudaError_t leaf_configure() {
+  static cudaError_t st = cudaFuncSetAttribute(gpk_leaf_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               LEAF_SMEM_BYTES);
+  return st;
 }
 
 struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err; };
@@ -121,6 +309,7 @@ struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info;
 static void chol_rec(CholCtx& c, int off, int n) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
+    if ((c.err = leaf_configure()) != cudaSuccess) return;
     gpk_leaf_potrf_inv_kernel<<<1, LEAF_THREADS, LEAF_SMEM_BYTES, c.st>>>(c.A, c.lda, c.Ml, c.Mu, c.ldm, off, c.info); GPK_LAUNCHED();
     c.err = cudaGetLastError();
     return;
