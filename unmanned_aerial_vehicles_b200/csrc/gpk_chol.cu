@@ -60,23 +60,25 @@ __device__ __forceinline__ void leaf_potrf_chunk(double (&r)[32], LeafSmem& sm, 
     buf[lane] = raw;
     __syncwarp();
     double d = buf[j];
+    // the other rows' raw column entries are fetched now so that they land during the rsqrt chain
+    const double* bj = buf + j;
+    double bl[W];
+#pragma unroll
+    for (int c = 1; c < W; ++c) bl[c] = bj[c];
     if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
       if (lane == 0) leaf_record(info, off + k0 + j + 1);
       d = __longlong_as_double(0x7ff8000000000000LL);
     }
-    // 1/sqrt(d) with one Newton step each on sqrt and reciprocal (no FP64 division on the critical path)
-    double dinv = rsqrt(d);
-    double ljj = d * dinv;
-    ljj = fma(0.5 * dinv, fma(-ljj, ljj, d), ljj);
-    dinv = fma(dinv, fma(-ljj, dinv, 1.0), dinv);
+    // rsqrt(double) is accurate to 1 ulp; l_jj = d * d^-1/2 (no FP64 division or sqrt on the critical path)
+    const double dinv = rsqrt(d);
+    const double ljj = d * dinv;
     const double li = (lane > j) ? raw * dinv : (lane == j ? ljj : 0.0);   // finished rows contribute nothing
     sm.S[(k0 + lane) * LF_LD + k0 + j] = li;
     sm.LT[j * 32 + lane] = li;
     if (lane == j) sm.dinv[k0 + j] = dinv;
     const double sc = -li * dinv;
-    const double* bj = buf + j;
 #pragma unroll
-    for (int c = 1; c < W; ++c) r[c - 1] = fma(sc, bj[c], r[c]);
+    for (int c = 1; c < W; ++c) r[c - 1] = fma(sc, bl[c], r[c]);
   }
 }
 __device__ __forceinline__ void leaf_diag_potrf(LeafSmem& sm, int k0, int lane, int off, int* info) {
@@ -170,9 +172,21 @@ gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ 
   const int tx = tid & 15, ty = tid >> 4;
   double* Ab = A + (size_t)off * lda + off;
   long long cyc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
-  for (int idx = tid; idx < GPK_TILE * GPK_TILE; idx += LEAF_THREADS) {
-    const int i = idx >> 7, c = idx & 127;
-    sm.S[i * LF_LD + c] = (c <= i) ? Ab[(size_t)i * lda + c] : 0.0;
+  // 16-byte loads, 8 in flight per thread (the block is 128 KB: latency-bound on one SM otherwise)
+#pragma unroll 1
+  for (int it = 0; it < 32; it += 8) {
+    double2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int idx = tid + (it + u) * LEAF_THREADS, i = idx >> 6, c = (idx & 63) * 2;
+      v[u] = (c <= i) ? *reinterpret_cast<const double2*>(Ab + (size_t)i * lda + c) : make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int idx = tid + (it + u) * LEAF_THREADS, i = idx >> 6, c = (idx & 63) * 2;
+      sm.S[i * LF_LD + c] = v[u].x;
+      sm.S[i * LF_LD + c + 1] = (c + 1 <= i) ? v[u].y : 0.0;
+    }
   }
   if (tid < 96) sm.col[0][tid] = 0.0;
   __syncthreads();
@@ -273,19 +287,28 @@ gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ 
   // ---- store L (lower), L^-1 (lower, zeros above), L^-T (upper, zeros below) -------------------------
   double* Ml = Mlow + (size_t)off * ldm + off;
   double* Mu = Mup + (size_t)off * ldm + off;
-  for (int idx = tid; idx < GPK_TILE * GPK_TILE; idx += LEAF_THREADS) {
-    const int i = idx >> 7, c = idx & 127;       // row i, column c of the output matrices
-    if (c <= i) Ab[(size_t)i * lda + c] = sm.S[i * LF_LD + c];
-    // Mlow[i][c] = M[i][c]
-    double m = 0.0;
-    if ((c >> 5) == (i >> 5)) m = sm.Mkk[i >> 5][(i & 31) * 33 + (c & 31)];
-    else if (c < i) m = sm.S[c * LF_LD + i];
-    Ml[(size_t)i * ldm + c] = m;
-    // Mup[i][c] = M[c][i]
-    double u = 0.0;
-    if ((c >> 5) == (i >> 5)) u = sm.Mkk[i >> 5][(c & 31) * 33 + (i & 31)];
-    else if (c > i) u = sm.S[i * LF_LD + c];
-    Mu[(size_t)i * ldm + c] = u;
+  // each thread produces 2 adjacent columns of one row per iteration (16-byte stores)
+#pragma unroll 4
+  for (int it = 0; it < 32; ++it) {
+    const int idx = tid + it * LEAF_THREADS, i = idx >> 6, c = (idx & 63) * 2;   // row i, columns c, c+1
+    const int bi = i >> 5, bc = c >> 5;
+    if (c <= i) {
+      double2 l = make_double2(sm.S[i * LF_LD + c], sm.S[i * LF_LD + c + 1]);
+      if (c + 1 <= i) *reinterpret_cast<double2*>(Ab + (size_t)i * lda + c) = l;
+      else Ab[(size_t)i * lda + c] = l.x;
+    }
+    double2 m = make_double2(0.0, 0.0), u = make_double2(0.0, 0.0);
+    if (bc == bi) {            // diagonal 32-block: Mkk holds explicit zeros above the diagonal
+      const double* mk = sm.Mkk[bi];
+      m = make_double2(mk[(i & 31) * 33 + (c & 31)], mk[(i & 31) * 33 + (c & 31) + 1]);
+      u = make_double2(mk[(c & 31) * 33 + (i & 31)], mk[((c & 31) + 1) * 33 + (i & 31)]);
+    } else if (bc < bi) {      // Mlow[i][c] = M[i][c] = S[c][i]
+      m = make_double2(sm.S[c * LF_LD + i], sm.S[(c + 1) * LF_LD + i]);
+    } else {                   // Mup[i][c] = M[c][i] = S[i][c]
+      u = make_double2(sm.S[i * LF_LD + c], sm.S[i * LF_LD + c + 1]);
+    }
+    *reinterpret_cast<double2*>(Ml + (size_t)i * ldm + c) = m;
+    *reinterpret_cast<double2*>(Mu + (size_t)i * ldm + c) = u;
   }
   LEAF_STAMP(6);
   if (tid == 0) {
