@@ -27,12 +27,22 @@ JITTER, NOISE0 = 1e-6, 0.01
 
 
 def make_data(n):
-    """SURVEY.md section 8(d) config 2"""
+    """SURVEY.md section 8(d) config 2 (config 4 with --n 50000 --targets 1: one single-output model per run)"""
     rng = np.random.default_rng(20251129)
     X = rng.standard_normal((n, D))
-    w = rng.standard_normal((D, T)) / 3
-    Y = np.sin(X @ w) + 0.1 * rng.standard_normal((n, T))
-    return X, Y
+    w = rng.standard_normal((D, 3)) / 3
+    Y = np.sin(X @ w) + 0.1 * rng.standard_normal((n, 3))
+    return X, np.ascontiguousarray(Y[:, :T])
+
+
+def workload_name(n):
+    tag = "config2" if n == 20000 else "config4-shaped" if n == 50000 else "custom"
+    return (f"{tag}: N={n} D={D} T={T} ARD-RBF+White LML+grad evaluation "
+            "(Gram + Cholesky/inverse + K^-1 + gradient), one theta per step")
+
+
+def metric_name(n):
+    return "gp_fit_lml_grad_evals_per_s_N%dk" % (n // 1000)
 
 
 def theta_sequence(rank, count):
@@ -93,10 +103,10 @@ def reference_arm(args):
     value = 1.0 / eval_s
     cores = os.cpu_count()
     line = {
-        "impl": "reference", "metric": "gp_fit_lml_grad_evals_per_s_N20k", "value": value, "unit": "evals/s",
+        "impl": "reference", "metric": metric_name(args.n), "value": value, "unit": "evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": eval_s * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"config2: N={args.n} D={D} T={T} ARD-RBF+White LML+grad evaluation",
+        "config": {"workload": workload_name(args.n),
                    "engine": "oracle port of sklearn 1.9.0 _gpr.py:583-656 on SciPy LAPACK/OpenBLAS"},
         "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -270,13 +280,12 @@ def b200_arm(args):
         h2d = int(X.nbytes + Y.nbytes)
         d2h = int(eng.out_len * 8 + 4)
         line = {
-            "metric": "gp_fit_lml_grad_evals_per_s_N20k", "value": world * K / dt, "unit": "evals/s",
+            "metric": metric_name(N), "value": world * K / dt, "unit": "evals/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"config2: N={N} D={D} T={T} ARD-RBF+White LML+grad evaluation "
-                                   "(Gram + Cholesky/inverse + K^-1 + gradient), one theta per step",
+            "config": {"workload": workload_name(N),
                        "sharding": "restarts x ranks, training set replicated, no collective in the data path",
-                       "l2": "inputs (3 x 3.2 GB factorisation buffers) larger than L2; no flush needed"},
+                       "l2": f"inputs (3 x {8e-9 * eng.NP ** 2:.1f} GB factorisation buffers) larger than L2; no flush needed"},
             "e2e": {"value": world * K / dt_e2e, "unit": "evals/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
@@ -318,13 +327,16 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=20000)
+    ap.add_argument("--size", "--n", dest="n", type=int, default=20000)  # torchrun's parser chokes on --n
+    ap.add_argument("--targets", type=int, default=3, choices=[1, 2, 3])
     ap.add_argument("--cpu-sample-n", type=int, default=0)
     ap.add_argument("--cpu-full", action="store_true")
     ap.add_argument("--predict-rows", type=int, default=81920)
     ap.add_argument("--full-fit", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    global T
+    T = args.targets
     if args.impl == "reference":
         reference_arm(args)
     else:
