@@ -232,9 +232,11 @@ def test_negative_variance_clamped_with_warning():
         assert any("Predicted variances smaller than 0" in str(x.message) for x in w)
 
 
-def test_large_n_properties():
-    """Size-independent checks at N=6000: L L^T = K on sampled rows, K alpha = y, K^-1 consistency."""
-    n, d, t = 6000, 9, 3
+@pytest.mark.parametrize("n", [6000, 20000])
+def test_large_n_properties(n):
+    """Size-independent checks up to BASELINE's full N=20000: L L^T = K on sampled rows, K alpha = y,
+    predictive mean at training rows = y - (noise + alpha) alpha_, finite-difference gradient."""
+    d, t = 9, 3
     X, Y = _data(n, d, t, seed=11)
     ls = np.full(d, 1.5)
     eng = DeviceGP(X, Y, 1e-6)
@@ -245,6 +247,10 @@ def test_large_n_properties():
     np.testing.assert_allclose(Krows @ a, Y[rows], rtol=0, atol=1e-8)
     L = eng.L_host()
     np.testing.assert_allclose(L[rows] @ L.T, Krows, rtol=0, atol=1e-12)
+    del L
+    mean, std, _, _ = eng.predict(X[rows], 0.0, 1.0, True)
+    np.testing.assert_allclose(mean, Y[rows] - (0.01 + 1e-6) * a[rows], rtol=0, atol=1e-8)
+    assert np.all(std > 0) and np.all(std < np.sqrt(1.01))
     lml, g_c, g_ls, g_noise = eng.lml(1.0 / ls, 1.0, 0.01, True)
     eps = 1e-5
     lp, *_ = eng.lml(1.0 / ls, 1.0, 0.01 * np.exp(eps), False)

@@ -7,6 +7,7 @@ through the C ABI (include/gpk.h).  Mirrors the arithmetic of sklearn/gaussian_p
 from __future__ import annotations
 
 import ctypes as C
+import threading
 
 import numpy as np
 
@@ -54,6 +55,7 @@ class DeviceGP:
         self.factored = None  # (inv_ls tuple, c, noise) of the factor currently held in Mlow/alpha
         self.a_holds_L = False
         self.launches = 0
+        self._plock = threading.Lock()   # predict() shares cached staging buffers: one caller at a time
 
     # -- helpers ---------------------------------------------------------------------------
     def _stream(self):
@@ -136,6 +138,38 @@ class DeviceGP:
             return K[: self.N, : self.N].cpu().numpy()
 
     # -- predict -------------------------------------------------------------------------------
+    def _predict_ws(self, MPmax: int):
+        """Device + pinned staging buffers for query chunks of up to MPmax rows.  Small ones (the 1..128-row
+        control-tick calls of simple_gp.py:187-201 / mpc.py:1490-1509) are kept between calls so a predict is
+        launches + one stream sync, with no allocation or pinning on the way."""
+        ws = getattr(self, "_pws", None)
+        if ws is not None and ws["MPmax"] >= MPmax:
+            return ws
+        t, NP, T = self.torch, self.NP, self.T
+        dev = self.device
+        ws = {"MPmax": MPmax,
+              "Ks": t.empty((MPmax, NP), dtype=t.float64, device=dev),
+              "out": t.empty((2, MPmax, T), dtype=t.float64, device=dev),        # [mean | std]
+              "rowsq": t.empty((MPmax, NP // 128), dtype=t.float64, device=dev),
+              "neg": t.zeros(1, dtype=t.int32, device=dev),
+              "xq": t.empty((MPmax, self.D), dtype=t.float64, device=dev),
+              "xq_pin": t.empty((MPmax, self.D), dtype=t.float64).pin_memory(),
+              "out_pin": t.empty((2, MPmax, T), dtype=t.float64).pin_memory(),
+              "neg_pin": t.zeros(1, dtype=t.int32).pin_memory()}
+        self._pws = ws if MPmax * NP * 8 <= (256 << 20) else None
+        return ws
+
+    def _target_scale(self, y_mean, y_std):
+        key = (tuple(np.broadcast_to(np.asarray(y_mean, dtype=np.float64), (self.T,)).tolist()),
+               tuple(np.broadcast_to(np.asarray(y_std, dtype=np.float64), (self.T,)).tolist()))
+        cached = getattr(self, "_yscale", None)
+        if cached is None or cached[0] != key:
+            t = self.torch
+            cached = (key, t.tensor(key[0], dtype=t.float64, device=self.device),
+                      t.tensor(key[1], dtype=t.float64, device=self.device))
+            self._yscale = cached
+        return cached[1], cached[2]
+
     def predict(self, Xq: np.ndarray, y_mean, y_std, return_std: bool, return_cov: bool = False, chunk_rows=None):
         """mean (M,T) [, std (M,T) | cov (M,M) un-normalised] for the factor currently held."""
         assert self.factored is not None, "factor() first"
@@ -153,32 +187,33 @@ class DeviceGP:
         std = np.empty((M, T)) if return_std else None
         cov = None
         neg_total = 0
-        with t.cuda.device(self.device):
+        with self._plock, t.cuda.device(self.device):
             st = self._stream()
-            ym = t.as_tensor(np.broadcast_to(np.asarray(y_mean, dtype=np.float64), (T,)).copy(), device=self.device)
-            ys = t.as_tensor(np.broadcast_to(np.asarray(y_std, dtype=np.float64), (T,)).copy(), device=self.device)
-            MPmax = min(chunk_rows, ((M + 127) // 128) * 128)
-            Ks = t.empty((MPmax, NP), dtype=t.float64, device=self.device)
-            mean_d = t.empty((MPmax, T), dtype=t.float64, device=self.device)
+            stream = t.cuda.current_stream(self.device)
+            ym, ys = self._target_scale(y_mean, y_std)
+            ws = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128))
+            Ks, mean_d, std_d, rowsq, neg_d = ws["Ks"], ws["out"][0], ws["out"][1], ws["rowsq"], ws["neg"]
             if return_std:
-                rowsq = t.empty((MPmax, NP // 128), dtype=t.float64, device=self.device)
-                std_d = t.empty((MPmax, T), dtype=t.float64, device=self.device)
-                neg_d = t.zeros(1, dtype=t.int32, device=self.device)
+                neg_d.zero_()
             inv_h = _lib.darr(inv_ls)
-            Xq_pin = t.from_numpy(Xq).pin_memory()
             for s in range(0, M, chunk_rows):
                 m = min(chunk_rows, M - s)
                 MP = ((m + 127) // 128) * 128
-                xq_d = Xq_pin[s:s + m].to(self.device, non_blocking=True)
+                ws["xq_pin"][:m].numpy()[...] = Xq[s:s + m]
+                xq_d = ws["xq"][:m]
+                xq_d.copy_(ws["xq_pin"][:m], non_blocking=True)
                 _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(self.X_d), self.N, self.D, inv_h, c,
                                                    self._p(Ks), MP, NP, st), "gpk_cross_gram")
                 _lib.check(self.lib.gpk_predict_mean(self._p(Ks), m, self.N, NP, self._p(self.alpha_d), T, self._p(ym),
                                                      self._p(ys), self._p(mean_d), st), "gpk_predict_mean")
+                ws["out_pin"][0, :m].copy_(mean_d[:m], non_blocking=True)
                 if return_std:
                     _lib.check(self.lib.gpk_predict_std(self._p(Ks), m, MP, self._p(self.Mlow_d), NP, c + noise,
                                                         self._p(ys), T, self._p(rowsq), self._p(std_d), self._p(neg_d),
                                                         st), "gpk_predict_std")
-                    std[s:s + m] = std_d[:m].cpu().numpy()
+                    ws["out_pin"][1, :m].copy_(std_d[:m], non_blocking=True)
+                    if s + m >= M:
+                        ws["neg_pin"].copy_(neg_d, non_blocking=True)
                 if return_cov:
                     V = t.empty((MP, NP), dtype=t.float64, device=self.device)
                     _lib.check(self.lib.gpk_gemm_nt(self._p(Ks), NP, self._p(self.Mlow_d), NP, self._p(V), NP, MP, NP,
@@ -190,7 +225,10 @@ class DeviceGP:
                                                     -1.0, 1, 0, 0, 0, st), "gpk_gemm_nt")
                     cov = Kqq[:m, :m].cpu().numpy()
                     cov[np.diag_indices_from(cov)] += noise
-                mean[s:s + m] = mean_d[:m].cpu().numpy()
+                stream.synchronize()                     # one sync per chunk: results are in the pinned buffers
+                mean[s:s + m] = ws["out_pin"][0, :m].numpy()
+                if return_std:
+                    std[s:s + m] = ws["out_pin"][1, :m].numpy()
             if return_std:
-                neg_total = int(neg_d.cpu()[0])
+                neg_total = int(ws["neg_pin"][0])
         return mean, std, cov, neg_total
