@@ -327,9 +327,27 @@ static cudaError_t leaf_configure() {
   return st;
 }
 
-struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err; };
+struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err;
+                 bool side; };
 
-static void chol_rec(CholCtx& c, int off, int n) {
+// Side streams for the one product of each level that nothing in the sub-recursion depends on
+// (Wt = M11^T-part * L21^T, needed only by M21 after rec(22)): it fills the SMs the small GEMMs and the
+// latency-bound leaves of rec(22) leave idle.  One fork event (re-recorded per level: a wait captures the state at
+// enqueue time) and one join event per recursion depth (one outstanding product per depth).
+#define GPK_CHOL_MAXDEPTH 24
+static cudaStream_t g_side[GPK_CHOL_MAXDEPTH];   // one per depth: a parent's large product must not queue ahead of its children's
+static cudaEvent_t g_fork = nullptr, g_join[GPK_CHOL_MAXDEPTH];
+static cudaError_t chol_side_init() {
+  if (g_fork) return cudaSuccess;
+  cudaError_t e;
+  for (int i = 0; i < GPK_CHOL_MAXDEPTH; ++i) {
+    if ((e = cudaStreamCreateWithFlags(&g_side[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&g_join[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+  }
+  return cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming);
+}
+
+static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
     if ((c.err = leaf_configure()) != cudaSuccess) return;
@@ -338,7 +356,7 @@ static void chol_rec(CholCtx& c, int off, int n) {
     return;
   }
   const int n1 = GPK_TILE * ((n / GPK_TILE + 1) / 2), n2 = n - n1, o2 = off + n1;
-  chol_rec(c, off, n1);
+  chol_rec(c, off, n1, depth + 1);
   if (c.err != cudaSuccess) return;
   double* A21 = c.A + (size_t)o2 * c.lda + off;
   double* Ml21 = c.Ml + (size_t)o2 * c.ldm + off;
@@ -350,18 +368,32 @@ static void chol_rec(CholCtx& c, int off, int n) {
   g.lower_only = 0; g.epilogue = GPK_EPI_STORE; g.rowsq = nullptr;
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
   if ((c.err = gpk_launch_copy_block(Ml21, c.ldm, A21, c.lda, n2, n1, c.st)) != cudaSuccess) return;
+  // Wt = Mt11 * L21^T  -> Mup12 (n1 x n2): independent of the A22 update and of rec(22) -> side stream
+  const bool fork = c.side && depth < GPK_CHOL_MAXDEPTH;
+  cudaStream_t ws = fork ? g_side[depth] : c.st;
+  if (fork) {
+    if ((c.err = cudaEventRecord(g_fork, c.st)) != cudaSuccess) return;          // after the L21 copy above
+    if ((c.err = cudaStreamWaitEvent(ws, g_fork, 0)) != cudaSuccess) return;
+  }
+  GpkGemmArgs w{};
+  w.A = c.Mu + (size_t)off * c.ldm + off; w.lda = c.ldm; w.B = A21; w.ldb = c.lda; w.C = Mu12; w.ldc = c.ldm;
+  w.M = n1; w.N = n2; w.K = n1; w.alpha = 1.0; w.a_tri = GPK_TRI_UPPER; w.epilogue = GPK_EPI_STORE;
+  if (fork) {
+    if ((c.err = gpk_launch_gemm_nt(w, ws)) != cudaSuccess) return;
+    if ((c.err = cudaEventRecord(g_join[depth], ws)) != cudaSuccess) return;
+  }
   // A22 -= L21 L21^T (lower tiles)
   g = GpkGemmArgs{};
   g.A = A21; g.lda = c.lda; g.B = A21; g.ldb = c.lda; g.C = c.A + (size_t)o2 * c.lda + o2; g.ldc = c.lda;
   g.M = n2; g.N = n2; g.K = n1; g.alpha = -1.0; g.accumulate = 1; g.lower_only = 1; g.epilogue = GPK_EPI_STORE;
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
-  chol_rec(c, o2, n2);
+  chol_rec(c, o2, n2, depth + 1);
   if (c.err != cudaSuccess) return;
-  // Wt = Mt11 * L21^T  -> Mup12 (n1 x n2)
-  g = GpkGemmArgs{};
-  g.A = c.Mu + (size_t)off * c.ldm + off; g.lda = c.ldm; g.B = A21; g.ldb = c.lda; g.C = Mu12; g.ldc = c.ldm;
-  g.M = n1; g.N = n2; g.K = n1; g.alpha = 1.0; g.a_tri = GPK_TRI_UPPER; g.epilogue = GPK_EPI_STORE;
-  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  if (fork) {
+    if ((c.err = cudaStreamWaitEvent(c.st, g_join[depth], 0)) != cudaSuccess) return;
+  } else {
+    if ((c.err = gpk_launch_gemm_nt(w, c.st)) != cudaSuccess) return;
+  }
   // M21 = -M22 * W  : C[m,j] = -sum_k M22[m,k] Wt[j,k]
   g = GpkGemmArgs{};
   g.A = c.Ml + (size_t)o2 * c.ldm + o2; g.lda = c.ldm; g.B = Mu12; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
@@ -375,7 +407,13 @@ cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, 
   if (NP % GPK_TILE) return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
-  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess};
+  // the side stream is bypassed while per-launch GEMM timing is on (overlapped durations would not add up)
+  bool side = false;
+  if (!g_gpk_prof.enabled && NP > 2 * GPK_TILE) {
+    if ((e = chol_side_init()) != cudaSuccess) return e;
+    side = true;
+  }
+  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side};
   chol_rec(c, 0, NP);
   return c.err;
 }
