@@ -74,6 +74,17 @@ int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* al
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
                     const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream);
 
+/* _gpr.py:370-500 in ONE call from HOST buffers (what simple_gp.py:194 and mpc.py:1490-1509 need per control
+ * tick): Xq_h (Mq x D) host -> mean_h (Mq x T) host [, std_h (Mq x T) host, *neg_h = rows whose variance was
+ * clamped at 0].  H2D, cross-Gram, mean, L^-1 contraction, std, D2H and one stream sync happen inside.
+ * X_d, alpha_d, Mlow_d, y_mean_d, y_std_d are the device-resident model; ws_d is device scratch of at least
+ * gpk_predict_workspace_doubles(MP = Mq rounded up to 128, NP, D, T) doubles.  std_h may be NULL (mean only). */
+size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T);
+int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
+                double noise, const double* alpha_d, int T, const double* Mlow_d, int NP, const double* y_mean_d,
+                const double* y_std_d, double* mean_h, double* std_h, int* neg_h, double* ws_d, size_t ws_doubles,
+                void* stream);
+
 /* utilities */
 int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream);
 int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream);

@@ -269,3 +269,23 @@ def test_from_sklearn_pickle_adoption():
     mg, sg = g.predict(X[:64] + 0.01, return_std=True)
     np.testing.assert_allclose(mg, ms, rtol=1e-6, atol=1e-10)
     np.testing.assert_allclose(sg, ss, rtol=0, atol=1e-8)
+
+
+@pytest.mark.parametrize("n", [700, 3000])
+def test_small_batch_variance_path_matches_gemm_path(n):
+    """Query batches of <= 32 rows take the triangular mat-vec variance kernel, larger ones the DMMA contraction
+    with the row-sum-of-squares epilogue: same numbers, and both equal the oracle (std 1e-8 abs)."""
+    X, Y = _data(n, 9, 3, seed=5)
+    ls = np.linspace(0.7, 1.9, 9)
+    eng = DeviceGP(X, Y, 1e-6)
+    assert eng.factor(1.0 / ls, 1.0, 0.02) == 0
+    Xq = X[:100] + 0.03
+    m_big, s_big, _, _ = eng.predict(Xq, 0.0, 1.0, True)
+    for lo, hi in [(0, 1), (1, 3), (3, 11), (11, 43 - 11), (32, 64), (64, 96), (96, 100)]:
+        m, s, _, _ = eng.predict(Xq[lo:hi], 0.0, 1.0, True)
+        np.testing.assert_allclose(m, m_big[lo:hi], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(s, s_big[lo:hi], rtol=0, atol=1e-11)
+    L, a = orc.factor(X, Y, ls, 1.0, 0.02, 1e-6)
+    m_o, s_o = orc.predict(Xq, X, L, a, ls, 1.0, 0.02)
+    np.testing.assert_allclose(m_big, m_o, rtol=1e-6, atol=1e-9)
+    assert np.max(np.abs(s_big - s_o)) <= 1e-8

@@ -13,6 +13,8 @@ cudaError_t gpk_launch_lml_grad(const double*, int, int, const GpkKernelParams&,
 cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*, int, const double*, const double*,
                                     double*, cudaStream_t);
 cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
+cudaError_t gpk_launch_small_rowsumsq(const double*, int, const double*, int, double*, cudaStream_t);
+#define GPK_SMALL_MQ 32   // query batches up to this size take the mat-vec variance path
 cudaError_t gpk_launch_extract_lower(const double*, int, double*, int, cudaStream_t);
 cudaError_t gpk_launch_pad_copy(const double*, int, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_copy_diag(const double*, int, int, double*, cudaStream_t);
@@ -132,11 +134,63 @@ int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* al
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
                     const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream) {
   if (MP % GPK_TILE || MP < Mq) return -3; if (NP % GPK_TILE) return -5;
+  if (Mq <= GPK_SMALL_MQ) {
+    GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks_d, Mq, rowsq_d, (cudaStream_t)stream));
+    GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / 32, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
+    return 0;
+  }
   GpkGemmArgs g{};
   g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
   g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
   GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
   GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
+  return 0;
+}
+
+size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T) {
+  if (MP < 1 || NP < 1 || D < 1 || T < 1) return 0;
+  return (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_TILE) + 2;
+}
+
+int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
+                double noise, const double* alpha_d, int T, const double* Mlow_d, int NP, const double* y_mean_d,
+                const double* y_std_d, double* mean_h, double* std_h, int* neg_h, double* ws_d, size_t ws_doubles,
+                void* stream) {
+  if (!Xq_h || !mean_h || !ws_d) return -1;
+  if (Mq < 1) return -2;
+  if (NP % GPK_TILE || NP < N) return -12;
+  if (T < 1) return -10;
+  const int MP = ((Mq + GPK_TILE - 1) / GPK_TILE) * GPK_TILE;
+  if (ws_doubles < gpk_predict_workspace_doubles(MP, NP, D, T)) return -19;
+  GpkKernelParams p;
+  if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -3;
+  cudaStream_t st = (cudaStream_t)stream;
+  double* Ks = ws_d;
+  double* xq = Ks + (size_t)MP * NP;
+  double* mean_d = xq + (size_t)MP * D;
+  double* std_d = mean_d + (size_t)MP * T;
+  double* rowsq = std_d + (size_t)MP * T;
+  int* neg_d = reinterpret_cast<int*>(rowsq + (size_t)MP * (NP / GPK_TILE));
+  GPK_CHECK(cudaMemcpyAsync(xq, Xq_h, sizeof(double) * (size_t)Mq * D, cudaMemcpyHostToDevice, st));
+  GPK_CHECK(gpk_launch_cross_gram(xq, Mq, X_d, N, D, p, Ks, MP, NP, st));
+  GPK_CHECK(gpk_launch_predict_mean(Ks, Mq, N, NP, alpha_d, T, y_mean_d, y_std_d, mean_d, st));
+  GPK_CHECK(cudaMemcpyAsync(mean_h, mean_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
+  if (std_h) {
+    GPK_CHECK(cudaMemsetAsync(neg_d, 0, sizeof(int), st));
+    if (Mq <= GPK_SMALL_MQ) {
+      GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks, Mq, rowsq, st));
+      GPK_CHECK(gpk_launch_predict_std(rowsq, NP / 32, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
+    } else {
+      GpkGemmArgs g{};
+      g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+      g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
+      GPK_CHECK(gpk_launch_gemm_nt(g, st));
+      GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
+    }
+    GPK_CHECK(cudaMemcpyAsync(std_h, std_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
+    if (neg_h) GPK_CHECK(cudaMemcpyAsync(neg_h, neg_d, sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
+  GPK_CHECK(cudaStreamSynchronize(st));
   return 0;
 }
 

@@ -226,6 +226,69 @@ __global__ void gpk_predict_std_kernel(const double* __restrict__ rowsq, int nti
   for (int t = 0; t < T; ++t) std_out[(size_t)q * lds + t] = sqrt(var * (y_std[t] * y_std[t]));
 }
 
+// Small query batches (the 1-row control-tick calls): ||L^-1 k*||^2 as a triangular mat-vec against up to MQ
+// cross-Gram rows at once, HBM/L2-bound on the N^2/2 doubles of L^-1 (the padded 128-row DMMA contraction would
+// run on NP/128 CTAs only).  CTA b owns rows [32b, 32b+32) (4 per warp) and writes
+// part[q, b] = sum_rows (Mlow[i, :i+1] . Ks[q, :i+1])^2  -- the layout gpk_predict_std_kernel sums.
+template <int MQ>
+__global__ void __launch_bounds__(256) gpk_small_rowsumsq_kernel(const double* __restrict__ Mlow, int NP,
+                                                                 const double* __restrict__ Ks, int mq,
+                                                                 double* __restrict__ part, int ldp) {
+  __shared__ double red[MQ][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double sq[MQ];
+#pragma unroll
+  for (int q = 0; q < MQ; ++q) sq[q] = 0.0;
+#pragma unroll 1
+  for (int rr = 0; rr < 4; ++rr) {
+    const int i = blockIdx.x * 32 + warp + 8 * rr;
+    const double* mrow = Mlow + (size_t)i * NP;
+    double acc[MQ];
+#pragma unroll
+    for (int q = 0; q < MQ; ++q) acc[q] = 0.0;
+    for (int k = 2 * lane; k <= i; k += 64) {
+      double2 m = *reinterpret_cast<const double2*>(mrow + k);
+      if (k + 1 > i) m.y = 0.0;
+#pragma unroll
+      for (int q = 0; q < MQ; ++q)
+        if (q < mq) {
+          const double2 v = *reinterpret_cast<const double2*>(Ks + (size_t)q * NP + k);
+          acc[q] = fma(m.x, v.x, fma(m.y, v.y, acc[q]));
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < MQ; ++q) {
+      double a = acc[q];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+      sq[q] = fma(a, a, sq[q]);
+    }
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < MQ; ++q) red[q][warp] = sq[q];
+  }
+  __syncthreads();
+  if (threadIdx.x < MQ && (int)threadIdx.x < mq) {
+    const double* r = red[threadIdx.x];
+    part[(size_t)threadIdx.x * ldp + blockIdx.x] = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+  }
+}
+// part: (Mq x NP/32); Mq <= 32 is handled 8 rows per launch
+cudaError_t gpk_launch_small_rowsumsq(const double* Mlow, int NP, const double* Ks, int Mq, double* part,
+                                      cudaStream_t st) {
+  const int nb = NP / 32;
+  for (int q0 = 0; q0 < Mq; q0 += 8) {
+    const int mq = Mq - q0 < 8 ? Mq - q0 : 8;
+    const double* ks = Ks + (size_t)q0 * NP;
+    double* pp = part + (size_t)q0 * nb;
+    if (mq == 1) gpk_small_rowsumsq_kernel<1><<<nb, 256, 0, st>>>(Mlow, NP, ks, mq, pp, nb);
+    else gpk_small_rowsumsq_kernel<8><<<nb, 256, 0, st>>>(Mlow, NP, ks, mq, pp, nb);
+    GPK_LAUNCHED();
+  }
+  return cudaGetLastError();
+}
+
 // dst (N x N, ld N) = lower triangle of src's leading N x N block, zeros above (scipy's L_ layout)
 __global__ void gpk_extract_lower_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int N) {
   int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;

@@ -139,24 +139,16 @@ class DeviceGP:
 
     # -- predict -------------------------------------------------------------------------------
     def _predict_ws(self, MPmax: int):
-        """Device + pinned staging buffers for query chunks of up to MPmax rows.  Small ones (the 1..128-row
-        control-tick calls of simple_gp.py:187-201 / mpc.py:1490-1509) are kept between calls so a predict is
-        launches + one stream sync, with no allocation or pinning on the way."""
+        """Device scratch for query chunks of up to MPmax rows (gpk_predict carves it).  Small ones (the 1..128-row
+        control-tick calls of simple_gp.py:187-201 / mpc.py:1490-1509) are kept between calls, so a predict is
+        ONE C-ABI call: H2D, four launches, D2H, one stream sync, no allocation on the way."""
         ws = getattr(self, "_pws", None)
-        if ws is not None and ws["MPmax"] >= MPmax:
+        if ws is not None and ws[0] >= MPmax:
             return ws
-        t, NP, T = self.torch, self.NP, self.T
-        dev = self.device
-        ws = {"MPmax": MPmax,
-              "Ks": t.empty((MPmax, NP), dtype=t.float64, device=dev),
-              "out": t.empty((2, MPmax, T), dtype=t.float64, device=dev),        # [mean | std]
-              "rowsq": t.empty((MPmax, NP // 128), dtype=t.float64, device=dev),
-              "neg": t.zeros(1, dtype=t.int32, device=dev),
-              "xq": t.empty((MPmax, self.D), dtype=t.float64, device=dev),
-              "xq_pin": t.empty((MPmax, self.D), dtype=t.float64).pin_memory(),
-              "out_pin": t.empty((2, MPmax, T), dtype=t.float64).pin_memory(),
-              "neg_pin": t.zeros(1, dtype=t.int32).pin_memory()}
-        self._pws = ws if MPmax * NP * 8 <= (256 << 20) else None
+        t = self.torch
+        n = int(self.lib.gpk_predict_workspace_doubles(MPmax, self.NP, self.D, self.T))
+        ws = (MPmax, t.empty(n, dtype=t.float64, device=self.device), n, np.zeros(1, dtype=np.int32))
+        self._pws = ws if n * 8 <= (256 << 20) else None
         return ws
 
     def _target_scale(self, y_mean, y_std):
@@ -189,46 +181,40 @@ class DeviceGP:
         neg_total = 0
         with self._plock, t.cuda.device(self.device):
             st = self._stream()
-            stream = t.cuda.current_stream(self.device)
             ym, ys = self._target_scale(y_mean, y_std)
-            ws = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128))
-            Ks, mean_d, std_d, rowsq, neg_d = ws["Ks"], ws["out"][0], ws["out"][1], ws["rowsq"], ws["neg"]
-            if return_std:
-                neg_d.zero_()
             inv_h = _lib.darr(inv_ls)
-            for s in range(0, M, chunk_rows):
-                m = min(chunk_rows, M - s)
-                MP = ((m + 127) // 128) * 128
-                ws["xq_pin"][:m].numpy()[...] = Xq[s:s + m]
-                xq_d = ws["xq"][:m]
-                xq_d.copy_(ws["xq_pin"][:m], non_blocking=True)
-                _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(self.X_d), self.N, self.D, inv_h, c,
-                                                   self._p(Ks), MP, NP, st), "gpk_cross_gram")
-                _lib.check(self.lib.gpk_predict_mean(self._p(Ks), m, self.N, NP, self._p(self.alpha_d), T, self._p(ym),
-                                                     self._p(ys), self._p(mean_d), st), "gpk_predict_mean")
-                ws["out_pin"][0, :m].copy_(mean_d[:m], non_blocking=True)
-                if return_std:
-                    _lib.check(self.lib.gpk_predict_std(self._p(Ks), m, MP, self._p(self.Mlow_d), NP, c + noise,
-                                                        self._p(ys), T, self._p(rowsq), self._p(std_d), self._p(neg_d),
-                                                        st), "gpk_predict_std")
-                    ws["out_pin"][1, :m].copy_(std_d[:m], non_blocking=True)
-                    if s + m >= M:
-                        ws["neg_pin"].copy_(neg_d, non_blocking=True)
-                if return_cov:
-                    V = t.empty((MP, NP), dtype=t.float64, device=self.device)
-                    _lib.check(self.lib.gpk_gemm_nt(self._p(Ks), NP, self._p(self.Mlow_d), NP, self._p(V), NP, MP, NP,
-                                                    NP, 1.0, 0, 0, 1, 0, st), "gpk_gemm_nt")
-                    Kqq = t.empty((MP, MP), dtype=t.float64, device=self.device)
-                    _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(xq_d), m, self.D, inv_h, c,
-                                                       self._p(Kqq), MP, MP, st), "gpk_cross_gram")
-                    _lib.check(self.lib.gpk_gemm_nt(self._p(V), NP, self._p(V), NP, self._p(Kqq), MP, MP, MP, NP,
-                                                    -1.0, 1, 0, 0, 0, st), "gpk_gemm_nt")
-                    cov = Kqq[:m, :m].cpu().numpy()
-                    cov[np.diag_indices_from(cov)] += noise
-                stream.synchronize()                     # one sync per chunk: results are in the pinned buffers
-                mean[s:s + m] = ws["out_pin"][0, :m].numpy()
-                if return_std:
-                    std[s:s + m] = ws["out_pin"][1, :m].numpy()
-            if return_std:
-                neg_total = int(ws["neg_pin"][0])
+            if not return_cov:
+                MPmax, ws_d, ws_n, neg_h = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128))
+                for s in range(0, M, chunk_rows):
+                    m = min(chunk_rows, M - s)
+                    rc = self.lib.gpk_predict(
+                        Xq[s:s + m].ctypes.data, m, self.D, self._p(self.X_d), self.N, inv_h, c, noise,
+                        self._p(self.alpha_d), T, self._p(self.Mlow_d), NP, self._p(ym), self._p(ys),
+                        mean[s:s + m].ctypes.data, std[s:s + m].ctypes.data if return_std else None,
+                        neg_h.ctypes.data, self._p(ws_d), ws_n, st)
+                    _lib.check(rc, "gpk_predict")
+                    if return_std:
+                        neg_total += int(neg_h[0])
+                return mean, std, None, neg_total
+            # covariance (sample_y): one chunk holding every query row
+            m = M
+            MP = ((m + 127) // 128) * 128
+            Ks = t.empty((MP, NP), dtype=t.float64, device=self.device)
+            mean_d = t.empty((MP, T), dtype=t.float64, device=self.device)
+            xq_d = t.as_tensor(Xq, device=self.device)
+            _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(self.X_d), self.N, self.D, inv_h, c,
+                                               self._p(Ks), MP, NP, st), "gpk_cross_gram")
+            _lib.check(self.lib.gpk_predict_mean(self._p(Ks), m, self.N, NP, self._p(self.alpha_d), T, self._p(ym),
+                                                 self._p(ys), self._p(mean_d), st), "gpk_predict_mean")
+            V = t.empty((MP, NP), dtype=t.float64, device=self.device)
+            _lib.check(self.lib.gpk_gemm_nt(self._p(Ks), NP, self._p(self.Mlow_d), NP, self._p(V), NP, MP, NP,
+                                            NP, 1.0, 0, 0, 1, 0, st), "gpk_gemm_nt")
+            Kqq = t.empty((MP, MP), dtype=t.float64, device=self.device)
+            _lib.check(self.lib.gpk_cross_gram(self._p(xq_d), m, self._p(xq_d), m, self.D, inv_h, c,
+                                               self._p(Kqq), MP, MP, st), "gpk_cross_gram")
+            _lib.check(self.lib.gpk_gemm_nt(self._p(V), NP, self._p(V), NP, self._p(Kqq), MP, MP, MP, NP,
+                                            -1.0, 1, 0, 0, 0, st), "gpk_gemm_nt")
+            cov = Kqq[:m, :m].cpu().numpy()
+            cov[np.diag_indices_from(cov)] += noise
+            mean[...] = mean_d[:m].cpu().numpy()
         return mean, std, cov, neg_total
