@@ -158,35 +158,34 @@ __global__ void gpk_lml_finalize_kernel(const double* __restrict__ partial, int 
                                         const double* __restrict__ L, size_t lstep, const double* __restrict__ y, int ldy,
                                         const double* __restrict__ alpha, int lda, GpkKernelParams p, int with_grad,
                                         double* __restrict__ out) {
+  // one CTA per reduced quantity q (grid = 1 + T [+ DP + 2]); fixed summation order -> deterministic
   __shared__ double sh[256];
   const int tid = threadIdx.x;
-  const int nq = 1 + T + (with_grad ? DPp2 : 0);
-  for (int q = 0; q < nq; ++q) {
-    double s = 0.0;
-    if (q == 0) { for (int i = tid; i < N; i += 256) s += log(L[(size_t)i * lstep]); }
-    else if (q <= T) { int t = q - 1; for (int i = tid; i < N; i += 256) s += y[(size_t)i * ldy + t] * alpha[(size_t)i * lda + t]; }
-    else { int d = q - 1 - T; for (int b = tid; b < nblocks; b += 256) s += partial[(size_t)b * DPp2 + d]; }
-    sh[tid] = s;
-    __syncthreads();
-    for (int o = 128; o; o >>= 1) { if (tid < o) sh[tid] += sh[tid + o]; __syncthreads(); }
-    if (tid == 0) {
-      double v = sh[0];
-      if (q == 0) out[1] = v;
-      else if (q <= T) out[2 + q - 1] = v;
-      else {
-        int d = q - 1 - T, DP = DPp2 - 2;
-        if (d < D) out[2 + T + 1 + d] = 0.5 * v;
-        else if (d == DP) out[2 + T] = 0.5 * v;
-        else if (d == DP + 1) out[2 + T + 1 + D] = 0.5 * p.noise * v;
-      }
-    }
-    __syncthreads();
-  }
+  const int q = blockIdx.x;
+  double s = 0.0;
+  if (q == 0) { for (int i = tid; i < N; i += 256) s += log(L[(size_t)i * lstep]); }
+  else if (q <= T) { int t = q - 1; for (int i = tid; i < N; i += 256) s += y[(size_t)i * ldy + t] * alpha[(size_t)i * lda + t]; }
+  else { int d = q - 1 - T; for (int b = tid; b < nblocks; b += 256) s += partial[(size_t)b * DPp2 + d]; }
+  sh[tid] = s;
+  __syncthreads();
+  for (int o = 128; o; o >>= 1) { if (tid < o) sh[tid] += sh[tid + o]; __syncthreads(); }
   if (tid == 0) {
-    double lml = 0.0;
-    for (int t = 0; t < T; ++t) lml += -0.5 * out[2 + t] - out[1] - 0.5 * (double)N * 1.8378770664093453;
-    out[0] = lml;
+    double v = sh[0];
+    if (q == 0) out[1] = v;
+    else if (q <= T) out[2 + q - 1] = v;
+    else {
+      int d = q - 1 - T, DP = DPp2 - 2;
+      if (d < D) out[2 + T + 1 + d] = 0.5 * v;
+      else if (d == DP) out[2 + T] = 0.5 * v;
+      else if (d == DP + 1) out[2 + T + 1 + D] = 0.5 * p.noise * v;
+    }
   }
+}
+// lml = sum_t (-1/2 y_t.alpha_t - sum log L_ii - N/2 log 2 pi)   (_gpr.py:613-617)
+__global__ void gpk_lml_combine_kernel(int N, int T, double* __restrict__ out) {
+  double lml = 0.0;
+  for (int t = 0; t < T; ++t) lml += -0.5 * out[2 + t] - out[1] - 0.5 * (double)N * 1.8378770664093453;
+  out[0] = lml;
 }
 
 // mean[q,t] = (sum_j Ks[q,j] alpha[j,t]) * y_std[t] + y_mean[t]; one warp per query row.
@@ -347,7 +346,8 @@ cudaError_t gpk_launch_lml_grad(const double* X, int N, int D, const GpkKernelPa
 #undef CALL
     }
   }
-  gpk_lml_finalize_kernel<<<1, 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out); GPK_LAUNCHED();
+  gpk_lml_finalize_kernel<<<1 + T + (with_grad ? DP + 2 : 0), 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out); GPK_LAUNCHED();
+  gpk_lml_combine_kernel<<<1, 1, 0, st>>>(N, T, out); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
