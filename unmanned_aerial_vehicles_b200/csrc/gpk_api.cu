@@ -14,7 +14,9 @@ cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*,
                                     double*, cudaStream_t);
 cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
 cudaError_t gpk_launch_small_rowsumsq(const double*, int, const double*, int, double*, cudaStream_t);
-#define GPK_SMALL_MQ 32   // query batches up to this size take the mat-vec variance path
+// Query batches this small take the mat-vec variance path: it re-reads L^-1 once per 8 rows, the DMMA contraction
+// pads to 128 rows and runs on NP/128 CTAs only, so the cross-over moves with N (measured at N=1000 and 20000).
+static inline bool gpk_small_batch(int Mq, int NP) { return Mq <= 8 || (Mq <= 32 && NP <= 4096); }
 cudaError_t gpk_launch_extract_lower(const double*, int, double*, int, cudaStream_t);
 cudaError_t gpk_launch_pad_copy(const double*, int, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_copy_diag(const double*, int, int, double*, cudaStream_t);
@@ -134,7 +136,7 @@ int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* al
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
                     const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream) {
   if (MP % GPK_TILE || MP < Mq) return -3; if (NP % GPK_TILE) return -5;
-  if (Mq <= GPK_SMALL_MQ) {
+  if (gpk_small_batch(Mq, NP)) {
     GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks_d, Mq, rowsq_d, (cudaStream_t)stream));
     GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / 32, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
     return 0;
@@ -177,7 +179,7 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
   GPK_CHECK(cudaMemcpyAsync(mean_h, mean_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
   if (std_h) {
     GPK_CHECK(cudaMemsetAsync(neg_d, 0, sizeof(int), st));
-    if (Mq <= GPK_SMALL_MQ) {
+    if (gpk_small_batch(Mq, NP)) {
       GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks, Mq, rowsq, st));
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / 32, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     } else {

@@ -22,7 +22,7 @@ __device__ __forceinline__ void load_scaled_rows(double (*s)[DP + 1], const doub
 
 // K[i,j] for the padded NP x NP buffer.  lower_only: only tiles with tj <= ti are produced.
 template <int DP>
-__global__ void __launch_bounds__(256) gpk_gram_kernel(const double* __restrict__ X, int ldx, int N, int NP,
+__global__ void __launch_bounds__(256, 2) gpk_gram_kernel(const double* __restrict__ X, int ldx, int N, int NP,
                                                        GpkKernelParams p, double* __restrict__ K, int ldk,
                                                        int lower_only) {
   const int tj = blockIdx.x, ti = blockIdx.y;
@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256) gpk_gram_kernel(const double* __restrict_
 
 // Kstar[q, j] = c * rbf(xq, xtrain_j)  (q < Mq, j < N), zero in the padding; MP x NP output.
 template <int DP>
-__global__ void __launch_bounds__(256) gpk_cross_gram_kernel(const double* __restrict__ Xq, int ldq, int Mq,
+__global__ void __launch_bounds__(256, 2) gpk_cross_gram_kernel(const double* __restrict__ Xq, int ldq, int Mq,
                                                              const double* __restrict__ X, int ldx, int N,
                                                              GpkKernelParams p, double* __restrict__ Ks, int ldk) {
   __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1];
@@ -212,6 +212,39 @@ __global__ void gpk_predict_mean_kernel(const double* __restrict__ Ks, int ldk, 
   }
 }
 
+// Few query rows (control-tick calls): one CTA per row, so a single row at N=20k is spread over 8 warps
+// (the warp-per-row kernel above takes 0.31 ms for it).  Fixed reduction order -> deterministic.
+__global__ void __launch_bounds__(256) gpk_predict_mean_cta_kernel(const double* __restrict__ Ks, int ldk, int N,
+                                                                   const double* __restrict__ alpha, int lda, int T,
+                                                                   const double* __restrict__ y_mean,
+                                                                   const double* __restrict__ y_std,
+                                                                   double* __restrict__ mean, int ldm) {
+  __shared__ double red[4][8];
+  const int row = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double* kr = Ks + (size_t)row * ldk;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    double acc[4] = {0, 0, 0, 0};
+    for (int j = threadIdx.x; j < N; j += 256) {
+      const double k = kr[j];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) if (t0 + t < T) acc[t] += k * alpha[(size_t)j * lda + t0 + t];
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      double s = acc[t];
+      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) red[t][warp] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 4 && t0 + (int)threadIdx.x < T) {
+      const double* r = red[threadIdx.x];
+      const double s = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+      mean[(size_t)row * ldm + t0 + threadIdx.x] = s * y_std[t0 + threadIdx.x] + y_mean[t0 + threadIdx.x];
+    }
+    __syncthreads();
+  }
+}
+
 // var = prior - sum_tiles rowsq ; negatives clamped to 0 and counted (sklearn _gpr.py:480-500)
 __global__ void gpk_predict_std_kernel(const double* __restrict__ rowsq, int ntiles, int Mq, double prior,
                                        const double* __restrict__ y_std, int T, double* __restrict__ std_out,
@@ -353,6 +386,10 @@ cudaError_t gpk_launch_lml_grad(const double* X, int N, int D, const GpkKernelPa
 
 cudaError_t gpk_launch_predict_mean(const double* Ks, int Mq, int N, int NP, const double* alpha, int T,
                                     const double* y_mean, const double* y_std, double* mean, cudaStream_t st) {
+  if (Mq <= 1024) {   // fewer than ~7 warps per SM with a warp per row: give each row a CTA instead
+    gpk_predict_mean_cta_kernel<<<Mq, 256, 0, st>>>(Ks, NP, N, alpha, T, T, y_mean, y_std, mean, T); GPK_LAUNCHED();
+    return cudaGetLastError();
+  }
   int blocks = (int)(((size_t)Mq * 32 + 255) / 256);
   gpk_predict_mean_kernel<<<blocks, 256, 0, st>>>(Ks, NP, Mq, N, alpha, T, T, y_mean, y_std, mean, T); GPK_LAUNCHED();
   return cudaGetLastError();
