@@ -70,7 +70,7 @@ int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* al
                      const double* y_std_d, double* mean_d, void* stream);
 
 /* _gpr.py:460-500: V = Ks L^-T, var = prior - rowsum(V^2) clamped at 0, std = sqrt(var * y_std^2).
- * rowsq_d: scratch MP x (NP/128).  *neg_d is incremented per clamped row (the caller warns). */
+ * rowsq_d: scratch MP x (NP/64).  *neg_d is incremented per clamped row (the caller warns). */
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
                     const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream);
 

@@ -145,13 +145,13 @@ int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, in
   g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
   g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
   GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
-  GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
+  GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_ROWSQ_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
   return 0;
 }
 
 size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T) {
   if (MP < 1 || NP < 1 || D < 1 || T < 1) return 0;
-  return (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_TILE) + 2;
+  return (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_ROWSQ_TILE) + 2;
 }
 
 int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
@@ -172,7 +172,7 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
   double* mean_d = xq + (size_t)MP * D;
   double* std_d = mean_d + (size_t)MP * T;
   double* rowsq = std_d + (size_t)MP * T;
-  int* neg_d = reinterpret_cast<int*>(rowsq + (size_t)MP * (NP / GPK_TILE));
+  int* neg_d = reinterpret_cast<int*>(rowsq + (size_t)MP * (NP / GPK_ROWSQ_TILE));
   GPK_CHECK(cudaMemcpyAsync(xq, Xq_h, sizeof(double) * (size_t)Mq * D, cudaMemcpyHostToDevice, st));
   GPK_CHECK(gpk_launch_cross_gram(xq, Mq, X_d, N, D, p, Ks, MP, NP, st));
   GPK_CHECK(gpk_launch_predict_mean(Ks, Mq, N, NP, alpha_d, T, y_mean_d, y_std_d, mean_d, st));
@@ -187,7 +187,7 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
       g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
       g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
       GPK_CHECK(gpk_launch_gemm_nt(g, st));
-      GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
+      GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_ROWSQ_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     }
     GPK_CHECK(cudaMemcpyAsync(std_h, std_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
     if (neg_h) GPK_CHECK(cudaMemcpyAsync(neg_h, neg_d, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #define GPK_TILE 128          // CTA tile edge of the DMMA GEMM and the Cholesky leaf
+#define GPK_ROWSQ_TILE 64     // column-tile width of the GPK_EPI_ROWSUMSQ partial sums (rowsq is M x N/64)
 #define GPK_MAXD 32           // max feature dimension supported by the kernel-function kernels
 #define GPK_MAXT 16           // max number of targets handled per launch of the small-T kernels
 
