@@ -322,30 +322,37 @@ cudaError_t gpk_leaf_cycles(long long* out_h) {
 }
 
 static cudaError_t leaf_configure() {
-  static cudaError_t st = cudaFuncSetAttribute(gpk_leaf_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               LEAF_SMEM_BYTES);
-  return st;
+  static bool done[GPK_MAX_DEV] = {false};
+  const int dev = gpk_current_device();
+  if (done[dev]) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(gpk_leaf_potrf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       LEAF_SMEM_BYTES);
+  if (e == cudaSuccess) done[dev] = true;
+  return e;
 }
 
-struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err;
-                 bool side; };
 
 // Side streams for the one product of each level that nothing in the sub-recursion depends on
 // (Wt = M11^T-part * L21^T, needed only by M21 after rec(22)): it fills the SMs the small GEMMs and the
 // latency-bound leaves of rec(22) leave idle.  One fork event (re-recorded per level: a wait captures the state at
 // enqueue time) and one join event per recursion depth (one outstanding product per depth).
 #define GPK_CHOL_MAXDEPTH 24
-static cudaStream_t g_side[GPK_CHOL_MAXDEPTH];   // one per depth: a parent's large product must not queue ahead of its children's
-static cudaEvent_t g_fork = nullptr, g_join[GPK_CHOL_MAXDEPTH];
-static cudaError_t chol_side_init() {
-  if (g_fork) return cudaSuccess;
+struct CholSide { cudaStream_t side[GPK_CHOL_MAXDEPTH]; cudaEvent_t join[GPK_CHOL_MAXDEPTH]; cudaEvent_t fork; bool ready; };
+static CholSide g_cs[GPK_MAX_DEV];   // one per device; a parent's large product must not queue ahead of its children's
+static cudaError_t chol_side_init(CholSide& cs) {
+  if (cs.ready) return cudaSuccess;
   cudaError_t e;
   for (int i = 0; i < GPK_CHOL_MAXDEPTH; ++i) {
-    if ((e = cudaStreamCreateWithFlags(&g_side[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
-    if ((e = cudaEventCreateWithFlags(&g_join[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaStreamCreateWithFlags(&cs.side[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&cs.join[i], cudaEventDisableTiming)) != cudaSuccess) return e;
   }
-  return cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming);
+  if ((e = cudaEventCreateWithFlags(&cs.fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+  cs.ready = true;
+  return cudaSuccess;
 }
+
+struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err;
+                 CholSide* side; };
 
 static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   if (c.err != cudaSuccess) return;
@@ -369,18 +376,18 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
   if ((c.err = gpk_launch_copy_block(Ml21, c.ldm, A21, c.lda, n2, n1, c.st)) != cudaSuccess) return;
   // Wt = Mt11 * L21^T  -> Mup12 (n1 x n2): independent of the A22 update and of rec(22) -> side stream
-  const bool fork = c.side && depth < GPK_CHOL_MAXDEPTH;
-  cudaStream_t ws = fork ? g_side[depth] : c.st;
+  const bool fork = c.side != nullptr && depth < GPK_CHOL_MAXDEPTH;
+  cudaStream_t ws = fork ? c.side->side[depth] : c.st;
   if (fork) {
-    if ((c.err = cudaEventRecord(g_fork, c.st)) != cudaSuccess) return;          // after the L21 copy above
-    if ((c.err = cudaStreamWaitEvent(ws, g_fork, 0)) != cudaSuccess) return;
+    if ((c.err = cudaEventRecord(c.side->fork, c.st)) != cudaSuccess) return;    // after the L21 copy above
+    if ((c.err = cudaStreamWaitEvent(ws, c.side->fork, 0)) != cudaSuccess) return;
   }
   GpkGemmArgs w{};
   w.A = c.Mu + (size_t)off * c.ldm + off; w.lda = c.ldm; w.B = A21; w.ldb = c.lda; w.C = Mu12; w.ldc = c.ldm;
   w.M = n1; w.N = n2; w.K = n1; w.alpha = 1.0; w.a_tri = GPK_TRI_UPPER; w.epilogue = GPK_EPI_STORE;
   if (fork) {
     if ((c.err = gpk_launch_gemm_nt(w, ws)) != cudaSuccess) return;
-    if ((c.err = cudaEventRecord(g_join[depth], ws)) != cudaSuccess) return;
+    if ((c.err = cudaEventRecord(c.side->join[depth], ws)) != cudaSuccess) return;
   }
   // A22 -= L21 L21^T (lower tiles)
   g = GpkGemmArgs{};
@@ -390,7 +397,7 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   chol_rec(c, o2, n2, depth + 1);
   if (c.err != cudaSuccess) return;
   if (fork) {
-    if ((c.err = cudaStreamWaitEvent(c.st, g_join[depth], 0)) != cudaSuccess) return;
+    if ((c.err = cudaStreamWaitEvent(c.st, c.side->join[depth], 0)) != cudaSuccess) return;
   } else {
     if ((c.err = gpk_launch_gemm_nt(w, c.st)) != cudaSuccess) return;
   }
@@ -408,10 +415,10 @@ cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, 
   cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
   // the side stream is bypassed while per-launch GEMM timing is on (overlapped durations would not add up)
-  bool side = false;
+  CholSide* side = nullptr;
   if (!g_gpk_prof.enabled && NP > 2 * GPK_TILE) {
-    if ((e = chol_side_init()) != cudaSuccess) return e;
-    side = true;
+    side = &g_cs[gpk_current_device()];
+    if ((e = chol_side_init(*side)) != cudaSuccess) return e;
   }
   CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side};
   chol_rec(c, 0, NP);

@@ -48,6 +48,10 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st);
 cudaError_t gpk_launch_copy_block(const double* src, int lds, double* dst, int ldd, int rows, int cols, cudaStream_t st);
 cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, int ldd, int rows, int cols, cudaStream_t st);
 
+// per-device one-time state (function attributes, side streams): indexed by the current device ordinal
+#define GPK_MAX_DEV 64
+static inline int gpk_current_device() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < GPK_MAX_DEV) ? d : 0; }
+
 extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)
 #define GPK_LAUNCHED() (++g_gpk_launches)
 // optional per-launch timing of the DMMA GEMM (bench.py roofline): event pairs around each launch

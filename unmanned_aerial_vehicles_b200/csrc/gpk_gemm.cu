@@ -158,12 +158,13 @@ __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt
 
 template <int TS, int WR, int WC>
 static cudaError_t launch_ts(const GpkGemmArgs& g, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[GPK_MAX_DEV] = {false};
+  const int dev = gpk_current_device();
+  if (!attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(gpk_gemm_nt_kernel<TS, WR, WC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          GEMM_SMEM_BYTES_TS(TS));
     if (e != cudaSuccess) return e;
-    attr_set = true;
+    attr_set[dev] = true;
   }
   dim3 grid(g.N / TS, g.M / TS);
   gpk_gemm_nt_kernel<TS, WR, WC><<<grid, 32 * WR * WC, GEMM_SMEM_BYTES_TS(TS), st>>>(g);
