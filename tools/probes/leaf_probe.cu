@@ -16,12 +16,11 @@ __global__ void __launch_bounds__(LEAF_THREADS, 1) probe_p1(const double* A, lon
     int i = idx >> 7, c = idx & 127;
     sm.S[i * LF_LD + c] = (c <= i) ? A[i * 128 + c] : 0.0;
   }
-  if (tid < 96) sm.col[0][tid] = 0.0;
+  if (tid < 128) sm.col[0][tid] = 0.0;
   __syncthreads();
   long long t0 = clock64();
-  if (mode == 0) { if (warp == 0) leaf_diag_potrf(sm, 0, lane, 0, info); __syncthreads(); }
-  else if (mode == 1) { if (warp == 0) leaf_diag_potrf(sm, 0, lane, 0, info); }          // no barrier
-  else if (mode == 2) { leaf_diag_potrf(sm, 0, lane, 0, info); }                         // all warps redundantly
+  if (warp < 4) leaf_diag_potrf4(sm, 0, lane, warp, 0, info);
+  if (mode == 0) __syncthreads();
   long long t1 = clock64();
   if (tid == 0) cyc[mode] = t1 - t0;
 }
@@ -33,7 +32,7 @@ int main() {
   cudaMemcpy(A, h.data(), 128 * 128 * 8, cudaMemcpyHostToDevice);
   cudaFuncSetAttribute(probe_p1, cudaFuncAttributeMaxDynamicSharedMemorySize, LEAF_SMEM_BYTES);
   for (int rep = 0; rep < 2; ++rep)
-    for (int mode = 0; mode < 3; ++mode) {
+    for (int mode = 0; mode < 2; ++mode) {
       probe_p1<<<1, LEAF_THREADS, LEAF_SMEM_BYTES>>>(A, cyc, info, mode);
       long long c[4]; cudaMemcpy(c, cyc, 32, cudaMemcpyDeviceToHost);
       printf("mode %d: P1 one 32-block = %lld cycles (%s)\n", mode, c[mode], cudaGetErrorString(cudaGetLastError()));

@@ -34,7 +34,7 @@ struct LeafSmem {
   double LT[32 * 32];      // LT[c][c2] = L_kk[c2][c] (transposed copy of the current diagonal block)
   double W[3][32 * 33];
   double dinv[GPK_TILE];   // 1 / L_ii
-  double col[2][48];       // P1: raw pivot column, double-buffered (reads run up to 15 entries past 32)
+  double col[2][64];       // P1: raw pivot column, double-buffered (reads of dead columns run up to index 63)
 };
 #define LEAF_SMEM_BYTES ((int)sizeof(LeafSmem))
 
@@ -43,53 +43,52 @@ __device__ __forceinline__ void leaf_record(int* info, int want) {
   if (old != 0 && old > want) atomicMin(info, want);
 }
 
-// P1: warp-synchronous potrf of the 32x32 block at (k0,k0); lane i owns row i in registers.
-// The code is kept SMALL (rolled loops): a fully unrolled sweep is ~3500 straight-line instructions executed
-// once by one warp and runs at instruction-fetch speed (measured 38k cycles per block).  Registers rotate so
-// that the active column is always r[0] (the FMA writes r[c-1]), which keeps the indexing static inside a
-// rolled loop.  Each step publishes the raw column through a double-buffered shared vector, so one
-// __syncwarp per column is the only synchronisation; the update uses r_c -= (a_i a_c) / d.
-template <int W>
-__device__ __forceinline__ void leaf_potrf_chunk(double (&r)[32], LeafSmem& sm, int k0, int jbase, int lane, int off,
-                                                 int* info) {
+// P1: potrf of the 32x32 block at (k0,k0) by FOUR warps.  In every warp lane i owns row i; warp w keeps the
+// columns c = w (mod 4) in 8 registers.  Step j: the owner warp (j mod 4) publishes the raw column through a
+// double-buffered shared vector, one 128-thread named barrier, then every warp scales by 1/sqrt(pivot) (1-ulp rsqrt,
+// no division) and updates its own live columns with r_c -= (a_i a_c)/d.  The code is kept SMALL (rolled over groups
+// of four steps): a fully unrolled sweep runs at instruction-fetch speed.  The owner rotates its registers as it
+// updates (the FMA writes r[t-1]), so the live column is always r[0] and the indexing stays static.
+// One warp did this in 356 cycles per column (8 k cycles of FMA issue + the serial chain); four take the chain only.
+__device__ __forceinline__ void leaf_diag_potrf4(LeafSmem& sm, int k0, int lane, int w, int off, int* info) {
+  double r[8];
+  const double* row = sm.S + (k0 + lane) * LF_LD + k0 + w;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) r[t] = row[4 * t];
 #pragma unroll 1
-  for (int s = 0; s < 8; ++s) {
-    const int j = jbase + s;
-    double* buf = sm.col[j & 1];
-    const double raw = r[0];
-    buf[lane] = raw;
-    __syncwarp();
-    double d = buf[j];
-    // the other rows' raw column entries are fetched now so that they land during the rsqrt chain
-    const double* bj = buf + j;
-    double bl[W];
+  for (int jj = 0; jj < 8; ++jj) {
 #pragma unroll
-    for (int c = 1; c < W; ++c) bl[c] = bj[c];
-    if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
-      if (lane == 0) leaf_record(info, off + k0 + j + 1);
-      d = __longlong_as_double(0x7ff8000000000000LL);
+    for (int s = 0; s < 4; ++s) {
+      const int j = 4 * jj + s;
+      double* buf = sm.col[j & 1];
+      if (w == s) buf[lane] = r[0];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const double raw = buf[lane];
+      double d = buf[j];
+      const double* bc = buf + 4 * (jj + (w < s ? 1 : 0)) + w;   // rows that match this warp's live columns
+      double bl[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) bl[t] = bc[4 * t];
+      if (!(d > 0.0)) {  // non-positive or NaN pivot: record and poison
+        if (w == 0 && lane == 0) leaf_record(info, off + k0 + j + 1);
+        d = __longlong_as_double(0x7ff8000000000000LL);
+      }
+      const double dinv = rsqrt(d);
+      const double ljj = d * dinv;
+      const double li = (lane > j) ? raw * dinv : (lane == j ? ljj : 0.0);   // finished rows contribute nothing
+      const double sc = -li * dinv;
+      if (w == s) {
+        sm.S[(k0 + lane) * LF_LD + k0 + j] = li;
+        sm.LT[j * 32 + lane] = li;
+        if (lane == j) sm.dinv[k0 + j] = dinv;
+#pragma unroll
+        for (int t = 1; t < 8; ++t) r[t - 1] = fma(sc, bl[t], r[t]);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) r[t] = fma(sc, bl[t], r[t]);
+      }
     }
-    // rsqrt(double) is accurate to 1 ulp; l_jj = d * d^-1/2 (no FP64 division or sqrt on the critical path)
-    const double dinv = rsqrt(d);
-    const double ljj = d * dinv;
-    const double li = (lane > j) ? raw * dinv : (lane == j ? ljj : 0.0);   // finished rows contribute nothing
-    sm.S[(k0 + lane) * LF_LD + k0 + j] = li;
-    sm.LT[j * 32 + lane] = li;
-    if (lane == j) sm.dinv[k0 + j] = dinv;
-    const double sc = -li * dinv;
-#pragma unroll
-    for (int c = 1; c < W; ++c) r[c - 1] = fma(sc, bl[c], r[c]);
   }
-}
-__device__ __forceinline__ void leaf_diag_potrf(LeafSmem& sm, int k0, int lane, int off, int* info) {
-  double r[32];
-  const double* row = sm.S + (k0 + lane) * LF_LD + k0;
-#pragma unroll
-  for (int c = 0; c < 32; ++c) r[c] = row[c];
-  leaf_potrf_chunk<32>(r, sm, k0, 0, lane, off, info);
-  leaf_potrf_chunk<24>(r, sm, k0, 8, lane, off, info);
-  leaf_potrf_chunk<16>(r, sm, k0, 16, lane, off, info);
-  leaf_potrf_chunk<8>(r, sm, k0, 24, lane, off, info);
 }
 
 // P2: rows below the diagonal block, one thread per row: x L_kk^T = a by forward substitution (axpy form)
@@ -188,14 +187,14 @@ gpk_leaf_potrf_inv_kernel(double* __restrict__ A, int lda, double* __restrict__ 
       sm.S[i * LF_LD + c + 1] = (c + 1 <= i) ? v[u].y : 0.0;
     }
   }
-  if (tid < 96) sm.col[0][tid] = 0.0;
+  if (tid < 128) sm.col[0][tid] = 0.0;
   __syncthreads();
   LEAF_STAMP(0);
   // ---- factorisation ------------------------------------------------------------------------------
 #pragma unroll 1
   for (int kb = 0; kb < 4; ++kb) {
     const int k0 = 32 * kb, base = k0 + 32;
-    if (warp == 0) leaf_diag_potrf(sm, k0, lane, off, info);
+    if (warp < 4) leaf_diag_potrf4(sm, k0, lane, warp, off, info);
     __syncthreads();
     LEAF_STAMP(1);
     if (kb == 3) break;
