@@ -15,6 +15,22 @@ def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
 
+class Fake:
+    """duck-typed estimator: the sharding helpers must not care what computes"""
+
+    def __init__(self, t=None):
+        self.t, self.seen = t, 0
+
+    def fit(self, X, y):
+        self.mu = float(y.mean())
+        return self
+
+    def predict(self, Xq, return_std=False):
+        self.seen += len(Xq)
+        m = Xq @ np.array([1.0, -2.0])
+        return (m, np.abs(m) + 1.0) if return_std else m
+
+
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
@@ -37,6 +53,18 @@ def _worker(rank, world, port, q):
     starts = [np.array([0.0, -2.0])] + [np.random.RandomState(1).uniform([-3, -8], [3, 1]) for _ in range(4)]
     res = parallel.run_sharded(run_one, starts)
     lo, hi = parallel.row_block(11, rank, world)
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_parallel_gloo import Fake          # module-level: all_gather_object pickles the fitted models
+    Xq = rng.standard_normal((11, 2))
+    fk = Fake()
+    m, sd = parallel.predict_sharded(fk, Xq, return_std=True)
+    assert fk.seen == hi - lo and np.array_equal(m, Xq @ np.array([1.0, -2.0])) and np.array_equal(sd, np.abs(m) + 1.0)
+    own = parallel.predict_sharded(Fake(), Xq, gather=False)
+    assert np.array_equal(own, (Xq @ np.array([1.0, -2.0]))[lo:hi])
+    Y3 = np.stack([y, 2 * y, y + 1.0], 1)
+    models = parallel.fit_sharded_outputs(lambda t: Fake(t), X, Y3)
+    assert [mm.t for mm in models] == [0, 1, 2] and np.allclose([mm.mu for mm in models], Y3.mean(0))
     q.put((rank, len(calls), [(list(map(float, a)), float(b)) for a, b in res], (lo, hi)))
     dist.barrier()
     dist.destroy_process_group()
