@@ -17,6 +17,10 @@
 #ifndef STAGES
 #define STAGES 2
 #endif
+#ifndef GEMM64_WR
+#define GEMM64_WR 2        // warp grid of the 64-tile kernel (warp tile 32 x 32)
+#define GEMM64_WC 2
+#endif
 #define GEMM_THREADS 256
 #define GEMM_SMEM_BYTES_TS(TS) (STAGES * 2 * (TS) * LDSM * 8)
 #define GPK_PROF_CAP 16384
@@ -197,7 +201,7 @@ cudaError_t gpk_launch_gemm_nt(const GpkGemmArgs& g, cudaStream_t st) {
     if (!g_ev0[g_gpk_prof.n]) { cudaEventCreate(&g_ev0[g_gpk_prof.n]); cudaEventCreate(&g_ev1[g_gpk_prof.n]); }
     cudaEventRecord(g_ev0[g_gpk_prof.n], st);
   }
-  cudaError_t le = ts == 128 ? launch_ts<128, GEMM_WR, GEMM_WC>(g, st) : ts == 64 ? launch_ts<64, 2, 2>(g, st) : launch_ts<32, 2, 2>(g, st);
+  cudaError_t le = ts == 128 ? launch_ts<128, GEMM_WR, GEMM_WC>(g, st) : ts == 64 ? launch_ts<64, GEMM64_WR, GEMM64_WC>(g, st) : launch_ts<32, 2, 2>(g, st);
   if (le != cudaSuccess) return le;
   GPK_LAUNCHED();
   if (prof) {
