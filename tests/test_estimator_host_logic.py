@@ -1,0 +1,159 @@
+"""Host logic of the sklearn-surface estimator (gpr.py) on CPU: the device engine is replaced by a test double that
+answers from the CPU oracle, so the restart draw, theta ordering, normalisation, output shapes, error behaviour and
+pickling can be compared with stock scikit-learn without a GPU.  The double lives here (tests may use the oracle;
+the product never does) -- the GPU tests in test_gpu_parity.py run the same comparisons through libgpk.so."""
+import pickle
+import warnings
+
+import numpy as np
+import pytest
+from sklearn.gaussian_process import GaussianProcessRegressor as SkGPR
+from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+
+from oracle import gp_oracle as orc
+from unmanned_aerial_vehicles_b200 import gpr as gpr_mod
+
+
+class OracleEngine:
+    """same interface as engine.DeviceGP (lml / factor / predict / alpha_host / L_host), NumPy arithmetic"""
+
+    def __init__(self, X, y2d, jitter, device=None):
+        self.X, self.y, self.jitter = np.array(X), np.array(y2d), float(jitter)
+        self.N, self.D = self.X.shape
+        self.T = self.y.shape[1]
+        self.factored, self.a_holds_L = None, False
+
+    def lml(self, inv_ls, c, noise, with_grad):
+        self.factored, self.a_holds_L = None, False
+        lml, g = orc.lml_and_grad(self.X, self.y, 1.0 / np.asarray(inv_ls), c, noise, self.jitter, eval_gradient=with_grad)
+        if not np.isfinite(lml):
+            return -np.inf, 0.0, np.zeros(self.D), 0.0
+        if not with_grad:
+            return lml, 0.0, np.zeros(self.D), 0.0
+        return lml, g["c"], g["ls"], g["noise"]
+
+    def factor(self, inv_ls, c, noise):
+        try:
+            self.L, self.alpha = orc.factor(self.X, self.y, 1.0 / np.asarray(inv_ls), c, noise, self.jitter)
+        except np.linalg.LinAlgError:
+            self.factored = None
+            return 1
+        self.factored, self.a_holds_L = (tuple(float(v) for v in inv_ls), float(c), float(noise)), True
+        return 0
+
+    def alpha_host(self): return self.alpha.copy()
+    def L_host(self): return self.L.copy()
+
+    def predict(self, Xq, y_mean, y_std, return_std, return_cov=False, chunk_rows=None):
+        inv_ls, c, noise = self.factored
+        ls = 1.0 / np.asarray(inv_ls)
+        if return_cov:
+            from scipy.linalg import solve_triangular
+            Ks = c * orc.rbf_cross(Xq, self.X, ls)
+            V = solve_triangular(self.L, Ks.T, lower=True)
+            cov = c * orc.rbf_cross(Xq, Xq, ls) + noise * np.eye(len(Xq)) - V.T @ V
+            return (Ks @ self.alpha) * y_std + y_mean, None, cov, 0
+        m, s = orc.predict(Xq, self.X, self.L, self.alpha, ls, c, noise, y_mean, y_std, return_std)
+        return m, s, None, 0
+
+
+@pytest.fixture(autouse=True)
+def _oracle_engine(monkeypatch):
+    monkeypatch.setattr(gpr_mod, "DeviceGP", OracleEngine)
+
+
+def _data(n, d, t, seed=0):
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((n, d))
+    Y = np.sin(X @ rng.standard_normal((d, t))) + 0.1 * rng.standard_normal((n, t))
+    return X, (Y if t > 1 else Y[:, 0])
+
+
+def _pair(kernel, X, Y, **kw):
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        s = SkGPR(kernel=kernel, **kw).fit(X, Y)
+        g = gpr_mod.GaussianProcessRegressor(kernel=kernel, **kw).fit(X, Y)
+    return s, g
+
+
+@pytest.mark.parametrize("kernel,t,normalize", [
+    (RBF(0.5) + WhiteKernel(0.1), 6, True),                                                       # simple_gp.py:167
+    (CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 4, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0)), 1, False),  # gp_trainer.py:163
+    (WhiteKernel(0.05) + CK(2.0) * RBF(1.5), 2, True),                                            # free constant, operands swapped
+])
+def test_fit_with_restarts_matches_sklearn(kernel, t, normalize):
+    X, Y = _data(70, 4, t, seed=3)
+    s, g = _pair(kernel, X, Y, alpha=1e-6, n_restarts_optimizer=2, normalize_y=normalize, random_state=0)
+    np.testing.assert_allclose(g.kernel_.theta, s.kernel_.theta, rtol=0, atol=2e-4)   # same starts, same optimiser
+    assert abs(g.log_marginal_likelihood_value_ - s.log_marginal_likelihood_value_) <= 1e-6 * abs(s.log_marginal_likelihood_value_)
+    assert str(g.kernel_)[:12] == str(s.kernel_)[:12] and g.n_features_in_ == 4
+    Xq = X[:9] + 0.1
+    ms, ss = s.predict(Xq, return_std=True)
+    mg, sg = g.predict(Xq, return_std=True)
+    assert mg.shape == ms.shape and sg.shape == ss.shape                               # squeeze rules (_gpr.py:453,497)
+    np.testing.assert_allclose(mg, ms, rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(sg, ss, rtol=1e-4, atol=1e-6)
+    assert g.predict(Xq).shape == s.predict(Xq).shape
+
+
+def test_fixed_theta_matches_sklearn_tightly():
+    X, Y = _data(90, 5, 3, seed=1)
+    k = CK(1.3) * RBF(np.linspace(0.7, 1.6, 5)) + WhiteKernel(0.03)
+    s, g = _pair(k, X, Y, alpha=1e-8, optimizer=None, normalize_y=True)
+    np.testing.assert_allclose(g.alpha_, s.alpha_, rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(g.L_, s.L_, rtol=0, atol=1e-12)
+    th = s.kernel_.theta + 0.1
+    ls_, gs_ = s.log_marginal_likelihood(th, eval_gradient=True)
+    lg_, gg_ = g.log_marginal_likelihood(th, eval_gradient=True)
+    assert abs(lg_ - ls_) <= 1e-10 * abs(ls_)
+    np.testing.assert_allclose(gg_, gs_, rtol=1e-8, atol=1e-9)                          # theta order: c, ls[0..5), noise
+    assert g.log_marginal_likelihood() == g.log_marginal_likelihood_value_
+    with pytest.raises(ValueError):
+        g.log_marginal_likelihood(None, eval_gradient=True)
+    mc, cc = g.predict(X[:5], return_cov=True)
+    ms, cs = s.predict(X[:5], return_cov=True)
+    np.testing.assert_allclose(cc, cs, rtol=0, atol=1e-9)
+    ys = g.sample_y(X[:4], n_samples=3, random_state=1)
+    assert ys.shape == s.sample_y(X[:4], n_samples=3, random_state=1).shape
+
+
+def test_error_behaviour_is_sklearns():
+    X, Y = _data(40, 2, 1, seed=2)
+    Xd = np.vstack([X, X[:5]])                       # duplicated rows, no noise, no jitter -> singular Gram
+    Yd = np.concatenate([Y, Y[:5]])
+    g = gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0), alpha=0.0, optimizer=None)
+    with pytest.raises(np.linalg.LinAlgError, match="not returning a positive definite matrix"):
+        g.fit(Xd, Yd)
+    g2 = gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0, (0.1, 10)), alpha=1e-6, optimizer=None).fit(X, Y)
+    g2._engine.jitter = 0.0
+    g2._engine.X = np.vstack([X[:1]] * len(X))       # force a non-PD evaluation
+    lml, grad = g2.log_marginal_likelihood(np.array([0.0]), eval_gradient=True)
+    assert lml == -np.inf and np.all(grad == 0)      # _gpr.py:592-593: no exception
+    with pytest.raises(ValueError, match="n_targets"):
+        gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0), n_targets=2).fit(X, Y)
+    with pytest.raises(ValueError, match="features"):
+        gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0), alpha=1e-6, optimizer=None).fit(X, Y).predict(np.zeros((3, 5)))
+    with pytest.raises(RuntimeError):
+        g2.predict(X[:2], return_std=True, return_cov=True)
+    with pytest.raises(NotImplementedError):
+        gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0), alpha=np.full(len(X), 1e-3)).fit(X, Y)
+    with pytest.raises(ValueError, match="finite"):
+        gpr_mod.GaussianProcessRegressor(kernel=RBF(1.0, (1e-2, np.inf)), n_restarts_optimizer=1, alpha=1e-6).fit(X, Y)
+
+
+def test_pickle_holds_host_arrays_only_and_round_trips():
+    X, Y = _data(50, 3, 2, seed=4)
+    g = gpr_mod.GaussianProcessRegressor(kernel=RBF(0.8) + WhiteKernel(0.05), alpha=1e-6, optimizer=None,
+                                         normalize_y=True).fit(X, Y)
+    m0, s0 = g.predict(X[:7] + 0.2, return_std=True)
+    blob = pickle.dumps({"gp_model": g, "training_count": 1})           # schema A (train_gp_offline.py:188-197)
+    assert b"OracleEngine" not in blob and b"DeviceGP" not in blob
+    g2 = pickle.loads(blob)["gp_model"]
+    assert g2._engine is None and isinstance(g2.L_, np.ndarray) and g2.L_.shape == (50, 50)
+    m1, s1 = g2.predict(X[:7] + 0.2, return_std=True)                    # device state rebuilt lazily
+    np.testing.assert_array_equal(m1, m0)
+    np.testing.assert_array_equal(s1, s0)
+    sk = SkGPR(kernel=RBF(0.8) + WhiteKernel(0.05), alpha=1e-6, optimizer=None, normalize_y=True).fit(X, Y)
+    g3 = gpr_mod.GaussianProcessRegressor.from_sklearn(pickle.loads(pickle.dumps(sk)))
+    np.testing.assert_allclose(g3.predict(X[:7] + 0.2), sk.predict(X[:7] + 0.2), rtol=1e-9, atol=1e-12)
