@@ -157,3 +157,12 @@ def test_pickle_holds_host_arrays_only_and_round_trips():
     sk = SkGPR(kernel=RBF(0.8) + WhiteKernel(0.05), alpha=1e-6, optimizer=None, normalize_y=True).fit(X, Y)
     g3 = gpr_mod.GaussianProcessRegressor.from_sklearn(pickle.loads(pickle.dumps(sk)))
     np.testing.assert_allclose(g3.predict(X[:7] + 0.2), sk.predict(X[:7] + 0.2), rtol=1e-9, atol=1e-12)
+
+
+def test_reference_callers_on_the_engine_double(golden_dir, tmp_path):
+    """The caller mirrors (SimpleQuadrotorGP wrapper trained on the reference CSV rows to the reference trainer's theta*,
+    batched horizon == 25 one-row calls, pickle schema A, per-output schema B) with the engine double: the same bodies
+    the GPU suite runs through libgpk.so."""
+    import test_callers
+    test_callers.test_wrapper_trains_like_reference_and_batches(golden_dir, tmp_path)
+    test_callers.test_per_output_schema_b(golden_dir)
