@@ -221,6 +221,12 @@ def test_four_ranks_gloo(grid, n):
     _run(4, grid, n)
 
 
+def test_eight_ranks_gloo_2x4():
+    """the grid the 8-GPU runs use by default (lcm(Pr, Pc) = 4: half of the transposed-exchange pieces are empty)"""
+    outs = _run(8, (2, 4), 1300)
+    assert [o[2] for o in outs[:4]] == [[0, 4, 8], [1, 5, 9], [2, 6, 10], [3, 7]]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,NB", [(1000, 256), (3000, 1024), (2048, 512)])
 def test_cuda_ops_single_rank_matches_engine(n, NB):
