@@ -166,3 +166,16 @@ def test_reference_callers_on_the_engine_double(golden_dir, tmp_path):
     import test_callers
     test_callers.test_wrapper_trains_like_reference_and_batches(golden_dir, tmp_path)
     test_callers.test_per_output_schema_b(golden_dir)
+
+
+def test_sklearn_estimator_checks_pass():
+    """scikit-learn's own estimator conformance suite (clone/get_params/set_params, input validation, dtype and
+    shape handling, pickling, fit idempotence, n_features_in_, multi-output ...) run on this estimator: what a caller
+    that swaps the import relies on without knowing it."""
+    from sklearn.utils.estimator_checks import check_estimator
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        results = check_estimator(gpr_mod.GaussianProcessRegressor(), on_fail=None)
+    failed = [(r["check_name"], str(r["exception"])[:200]) for r in results if r["status"] == "failed"]
+    assert not failed, failed
+    assert sum(r["status"] == "passed" for r in results) >= 50

@@ -229,6 +229,11 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
             raise ValueError(f"Unknown optimizer {self.optimizer}.")
         return theta_opt, func_min
 
+    def __sklearn_tags__(self):
+        tags = super().__sklearn_tags__()
+        tags.requires_fit = False        # predict before fit answers from the prior (_gpr.py:417-443, :676-679)
+        return tags
+
     # -- pickling: host NumPy only, device state rebuilt lazily ----------------------------------
     def __getstate__(self):
         state = dict(self.__dict__)
