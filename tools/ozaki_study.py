@@ -71,17 +71,24 @@ def leaf(A):
     return L, M
 
 
-def chol_inv(A, gemm, nb=128):
-    """same recursion as csrc/gpk_chol.cu chol_rec: returns (L, M = L^-1), every product through gemm(A, B) = A B^T"""
+def chol_inv(A, gemm, nb=128, gemm_inv=None, gemm_tail=None, on_tail=True):
+    """same recursion as csrc/gpk_chol.cu chol_rec: returns (L, M = L^-1).  The factor's products (L21, trailing
+    update) go through gemm(A, B) = A B^T; the inverse's (Wt, M21) through gemm_inv (default: the same), except on
+    the right-most path of the recursion (root, root.22, root.22.22, ...), whose inverse blocks feed no later
+    L21 -- only K^-1 and predict -- and go through gemm_tail (default: gemm_inv).  That path holds 6/7 of the
+    inverse's flops (N^3/4 at the root, an eighth of that per level down)."""
+    gemm_inv = gemm_inv or gemm
+    gemm_tail = gemm_tail or gemm_inv
     n = len(A)
     if n <= nb:
         return leaf(A)
     h = (n // 2 + nb - 1) // nb * nb
-    L11, M11 = chol_inv(A[:h, :h], gemm, nb)
+    L11, M11 = chol_inv(A[:h, :h], gemm, nb, gemm_inv, gemm_tail, False)
     L21 = gemm(A[h:, :h], M11)                         # A21 M11^T
-    L22, M22 = chol_inv(A[h:, h:] - gemm(L21, L21), gemm, nb)
-    Wt = gemm(M11.T.copy(), L21)                       # (M11^T) L21^T = (L21 M11)^T
-    M21 = -gemm(M22, Wt)                               # -M22 (L21 M11)
+    L22, M22 = chol_inv(A[h:, h:] - gemm(L21, L21), gemm, nb, gemm_inv, gemm_tail, on_tail)
+    gi = gemm_tail if on_tail else gemm_inv
+    Wt = gi(M11.T.copy(), L21)                         # (M11^T) L21^T = (L21 M11)^T
+    M21 = -gi(M22, Wt)                                 # -M22 (L21 M11)
     L = np.zeros((n, n)); M = np.zeros((n, n))
     L[:h, :h], L[h:, :h], L[h:, h:] = L11, L21, L22
     M[:h, :h], M[h:, :h], M[h:, h:] = M11, M21, M22
@@ -135,13 +142,36 @@ def case(name, X, Y, ls, c, noise, jitter, Xq, slices):
             # also: FP64 factor, emulated contraction only (what a predict-only or LAUUM-only use would see)
             ref["M"], ref["Ks"] = M, Ks
             continue
+        rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
         Vp = g(ref["Ks"], ref["M"])
         std_p = np.sqrt(np.maximum((c + noise) - np.sum(Vp * Vp, axis=1), 0.0))
         Kinv_p = g(ref["M"].T.copy(), ref["M"].T.copy())
         grad_p = gradient(X, ls, c, noise, ref["alpha"], Kinv_p)
-        rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+        # FP64 factor products, emulated inverse products + LAUUM (2/3 of the step's flops)
+        Lm, Mm = chol_inv(K, make_gemm(0), gemm_inv=g)
+        am = Mm.T @ (Mm @ Y)
+        lml_m = float(np.sum(-0.5 * np.einsum("ik,ik->k", Y, am)) - Y.shape[1] * np.log(np.diag(Lm)).sum()
+                      - Y.shape[1] * N / 2 * np.log(2 * np.pi))
+        grad_m = gradient(X, ls, c, noise, am, g(Mm.T.copy(), Mm.T.copy()))
+        Vm = g(ref["Ks"], Mm)
+        std_m = np.sqrt(np.maximum((c + noise) - np.sum(Vm * Vm, axis=1), 0.0))
+        # FP64 everywhere the factor reads; emulated right-most-path inverse blocks + LAUUM + predict.
+        # alpha comes from the FP64 factor (substitution over L, as the product would do it), not from M.
+        f64 = make_gemm(0)
+        Lt, Mt = chol_inv(K, f64, gemm_inv=f64, gemm_tail=g)
+        grad_t = gradient(X, ls, c, noise, ref["alpha"], g(Mt.T.copy(), Mt.T.copy()))
+        Vt = g(ref["Ks"], Mt)
+        std_t = np.sqrt(np.maximum((c + noise) - np.sum(Vt * Vt, axis=1), 0.0))
+        assert np.array_equal(Lt, ref["L"])
         row = {
             "case": name, "N": N, "slices": S, "products": S * (S + 1) // 2,
+            "tail_lauum_grad_rel": rel(grad_t, ref["grad"]),
+            "tail_lauum_predict_std_abs": float(np.max(np.abs(std_t - ref["std"]))),
+            "inv_lauum_L_abs": float(np.max(np.abs(Lm - ref["L"]))),
+            "inv_lauum_alpha_rel": float(np.max(np.abs(am - ref["alpha"])) / np.max(np.abs(ref["alpha"]))),
+            "inv_lauum_lml_rel": abs(lml_m - ref["lml"]) / abs(ref["lml"]),
+            "inv_lauum_grad_rel": rel(grad_m, ref["grad"]),
+            "inv_lauum_predict_std_abs": float(np.max(np.abs(std_m - ref["std"]))),
             "predict_only_std_abs": float(np.max(np.abs(std_p - ref["std"]))),
             "lauum_only_grad_rel": rel(grad_p, ref["grad"]),
             "all_gemms_L_abs": float(np.max(np.abs(L - ref["L"]))),
