@@ -107,6 +107,22 @@ int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pa
 /* *sum_d += sum_i log A[i,i], i < n */
 int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
 
+/* EXPERIMENTAL (not called by the estimator yet): FP64-accurate C = alpha * A * B^T on the tcgen05
+ * INT8 pipe.  Operands are pre-split into S int8 slice planes with one power-of-two scale per row:
+ *   a[i,k] = mu[i] * sum_s planes[s][i][k] * 2^-(6+7s),   |planes| <= 64,   planes laid out [S][rowsP][KP], K contiguous.
+ * gpk_i8_slice: src_d (rows x K, leading dimension ld; tri = 0 full, 1 lower, 2 upper: only that triangle is read)
+ *   -> planes_d (S * rowsP * KP bytes, zero padded), mu_d (rowsP).  rowsP multiple of 64 (128 for a left operand),
+ *   KP multiple of 64.
+ * gpk_i8_gemm_nt: A planes (M x KP), B planes (N x KP), S(S+1)/2 exact slice products in int32 tensor-memory
+ *   accumulators, combined in FP64.  Same meaning of accumulate / a_tri / b_tri / lower_only as gpk_gemm_nt.
+ *   rowsq_d != NULL: nothing is stored to C; rowsq_d (M x N/64) receives per-tile row sums of squares (predict's
+ *   variance contraction).  M multiple of 128, N and KP multiples of 64, S * KP < 2^19. */
+int gpk_i8_slice(const double* src_d, int ld, int rows, int K, int tri, int S, signed char* planes_d, int rowsP, int KP,
+                 double* mu_d, void* stream);
+int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const signed char* Bq_d, const double* mu_b_d,
+                   int N, int KP, int S, double* C_d, int ldc, double alpha, int accumulate, int a_tri, int b_tri,
+                   int lower_only, double* rowsq_d, void* stream);
+
 /* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
  * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */
 unsigned long long gpk_launch_count(void);

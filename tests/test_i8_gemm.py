@@ -1,0 +1,174 @@
+"""EXPERIMENTAL int8-sliced (Ozaki) FP64 contraction on the tcgen05 INT8 pipe: csrc/gpk_i8gemm.cu.
+
+CPU part (always runs): the NumPy statement of the splitting arithmetic -- what the CUDA kernels must reproduce bit
+for bit -- reconstructs its input to the promised number of bits and gives FP64-class products at 8 slices.
+
+GPU part: written in round 1 after the GPU budget was spent, so the kernels have compiled but never run.  It is
+therefore opt-in (GPK_I8_EXPERIMENT=1) until its first green run on a B200; the default GPU suite does not depend
+on it and nothing on the estimator's path calls these entry points yet.
+"""
+import os
+
+import numpy as np
+import pytest
+
+
+def split(A, S):
+    """rows of A -> mu (power of two, |a|/mu < 1), S integer-valued slices (|q| <= 64), cumulative bit shifts"""
+    amax = np.max(np.abs(A), axis=1) if A.shape[1] else np.zeros(A.shape[0])
+    _, e = np.frexp(amax)                                  # amax = f * 2^e, f in [0.5, 1)
+    mu = np.where(amax > 0, np.ldexp(1.0, e), 1.0)
+    r = A / mu[:, None]
+    qs, shifts, bits = [], [], 0
+    for s in range(S):
+        b = 6 if s == 0 else 7
+        r = r * 2.0 ** b
+        q = np.rint(r)
+        r = r - q
+        bits += b
+        qs.append(q)
+        shifts.append(bits)
+    return mu, qs, shifts
+
+
+def gemm_nt_sliced(A, B, S, alpha=1.0):
+    """alpha * A B^T through S slices per operand, products with s + t <= S - 1 (0-based), grouped by s + t"""
+    mua, qa, sa = split(A, S)
+    mub, qb, sb = split(B, S)
+    C = np.zeros((A.shape[0], B.shape[0]))
+    for g in range(S - 1, -1, -1):                          # smallest scale first, like the kernel's epilogue
+        P = np.zeros_like(C)
+        for s in range(g + 1):
+            P += qa[s] @ qb[g - s].T                        # exact small integers
+        C += P * 2.0 ** (-(12 + 7 * g))
+    return (C * (alpha * mua)[:, None]) * mub[None, :]
+
+
+def _wide(rng, m, k):
+    """rows with very different magnitudes and entries spanning many binades inside a row"""
+    return rng.standard_normal((m, k)) * np.exp(3 * rng.standard_normal((m, k))) * np.exp(10 * rng.standard_normal((m, 1)))
+
+
+def test_split_reconstructs_to_the_promised_bits():
+    rng = np.random.default_rng(0)
+    A = _wide(rng, 37, 200)
+    A[5] = 0.0
+    A[6, 3] = 2.0 ** -7                                      # exact power of two as the row maximum
+    A[6, :3] = 0; A[6, 4:] = 0
+    for S in (1, 4, 7, 8):
+        mu, qs, sh = split(A, S)
+        assert max(np.max(np.abs(q)) for q in qs) <= 64 and all(np.all(q == np.rint(q)) for q in qs)
+        assert np.all(np.log2(mu) == np.rint(np.log2(mu))) and np.all(np.abs(A) < mu[:, None])
+        R = sum(q * 2.0 ** -b for q, b in zip(qs, sh)) * mu[:, None]
+        assert np.max(np.abs(R - A) / mu[:, None]) <= 2.0 ** -(sh[-1] + 1)
+
+
+def test_sliced_product_reaches_fp64_class_accuracy():
+    rng = np.random.default_rng(1)
+    A, B = rng.standard_normal((96, 512)), rng.standard_normal((80, 512))
+    ref = A @ B.T
+    scale = np.sqrt(np.sum(A * A, 1))[:, None] * np.sqrt(np.sum(B * B, 1))[None, :]
+    errs = {S: np.max(np.abs(gemm_nt_sliced(A, B, S) - ref) / scale) for S in (4, 6, 8)}
+    assert errs[4] < 1e-5 and errs[6] < 1e-9 and errs[8] < 2e-14
+    assert errs[8] < errs[6] < errs[4]
+
+
+# ------------------------------------------------------------------------------------------------ GPU (opt-in)
+_gated = pytest.mark.skipif(os.environ.get("GPK_I8_EXPERIMENT") != "1",
+                            reason="experimental tcgen05 int8 path: set GPK_I8_EXPERIMENT=1 (never run on a GPU yet)")
+
+
+def _device_sliced(torch, lib, A, S, row_mult, tri=0):
+    rows, K = A.shape
+    rowsP = -(-rows // row_mult) * row_mult
+    KP = -(-K // 64) * 64
+    src = torch.from_numpy(np.ascontiguousarray(A)).cuda()
+    planes = torch.empty((S, rowsP, KP), dtype=torch.int8, device="cuda")
+    mu = torch.empty(rowsP, dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.gpk_i8_slice(src.data_ptr(), K, rows, K, tri, S, planes.data_ptr(), rowsP, KP, mu.data_ptr(), st)
+    assert rc == 0, rc
+    return planes, mu, rowsP, KP
+
+
+@pytest.mark.gpu
+@_gated
+@pytest.mark.parametrize("S", [1, 4, 7, 8])
+def test_device_slices_are_bit_identical(S):
+    import torch
+    from unmanned_aerial_vehicles_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(2)
+    A = _wide(rng, 150, 300)
+    A[7] = 0.0
+    planes, mu, rowsP, KP = _device_sliced(torch, lib, A, S, 128)
+    mu_h, qs, _ = split(A, S)
+    got = planes.cpu().numpy()
+    assert np.array_equal(mu.cpu().numpy()[:150], mu_h) and np.all(mu.cpu().numpy()[150:] == 1.0)
+    for s in range(S):
+        assert np.array_equal(got[s, :150, :300], qs[s].astype(np.int8))
+    assert not got[:, 150:, :].any() and not got[:, :, 300:].any()
+
+
+@pytest.mark.gpu
+@_gated
+@pytest.mark.parametrize("m,n,k,S", [(128, 64, 64, 1), (128, 64, 256, 4), (384, 320, 1000, 7), (256, 192, 2048, 8)])
+def test_device_product_is_bit_identical_to_the_numpy_statement(m, n, k, S):
+    import torch
+    from unmanned_aerial_vehicles_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(3)
+    A, B = _wide(rng, m, k), _wide(rng, n, k)
+    pa, mua, MP, KP = _device_sliced(torch, lib, A, S, 128)
+    pb, mub, NP, _ = _device_sliced(torch, lib, B, S, 64)
+    C = torch.full((MP, NP), float("nan"), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.gpk_i8_gemm_nt(pa.data_ptr(), mua.data_ptr(), MP, pb.data_ptr(), mub.data_ptr(), NP, KP, S,
+                            C.data_ptr(), NP, -1.0, 0, 0, 0, 0, None, st)
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    want = gemm_nt_sliced(A, B, S, alpha=-1.0)
+    got = C.cpu().numpy()
+    assert np.array_equal(got[:m, :n], want)
+    assert not got[m:, :].any() and not got[:, n:].any()
+    # accumulate on top, and the row-sum-of-squares epilogue
+    rc = lib.gpk_i8_gemm_nt(pa.data_ptr(), mua.data_ptr(), MP, pb.data_ptr(), mub.data_ptr(), NP, KP, S,
+                            C.data_ptr(), NP, 1.0, 1, 0, 0, 0, None, st)
+    assert rc == 0, rc
+    assert np.array_equal(C.cpu().numpy()[:m, :n], want + gemm_nt_sliced(A, B, S, alpha=1.0))
+    rowsq = torch.zeros((MP, NP // 64), dtype=torch.float64, device="cuda")
+    rc = lib.gpk_i8_gemm_nt(pa.data_ptr(), mua.data_ptr(), MP, pb.data_ptr(), mub.data_ptr(), NP, KP, S,
+                            None, 0, 1.0, 0, 0, 0, 0, rowsq.data_ptr(), st)
+    assert rc == 0, rc
+    v = gemm_nt_sliced(A, B, S)
+    np.testing.assert_allclose(rowsq.cpu().numpy().sum(1)[:m], np.sum(v * v, 1), rtol=1e-13)
+
+
+@pytest.mark.gpu
+@_gated
+def test_device_triangular_trimming_and_lower_only():
+    import torch
+    from unmanned_aerial_vehicles_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(4)
+    n, S = 512, 7
+    U = np.triu(rng.standard_normal((n, n))) + 4 * np.eye(n)          # like L^-T: K^-1 = U U^T, lower tiles only
+    pu, mu, NP, KP = _device_sliced(torch, lib, U, S, 128, tri=2)
+    C = torch.zeros((NP, NP), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.gpk_i8_gemm_nt(pu.data_ptr(), mu.data_ptr(), NP, pu.data_ptr(), mu.data_ptr(), NP, KP, S,
+                            C.data_ptr(), NP, 1.0, 0, 2, 2, 1, None, st)
+    assert rc == 0, rc
+    want = gemm_nt_sliced(U, U, S)
+    got = C.cpu().numpy()
+    low = np.tril_indices(n)
+    assert np.array_equal(got[low], want[low])
+    Lo = np.tril(rng.standard_normal((n, n)))                          # like predict: Ks L^-T with L^-1 lower
+    Q = rng.standard_normal((256, n))
+    pq, mq, MP, _ = _device_sliced(torch, lib, Q, S, 128)
+    pl, ml, _, _ = _device_sliced(torch, lib, Lo, S, 64, tri=1)
+    V = torch.zeros((MP, NP), dtype=torch.float64, device="cuda")
+    rc = lib.gpk_i8_gemm_nt(pq.data_ptr(), mq.data_ptr(), MP, pl.data_ptr(), ml.data_ptr(), NP, KP, S,
+                            V.data_ptr(), NP, 1.0, 0, 0, 1, 0, None, st)
+    assert rc == 0, rc
+    assert np.array_equal(V.cpu().numpy()[:256, :n], gemm_nt_sliced(Q, Lo, S))

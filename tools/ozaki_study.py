@@ -8,7 +8,7 @@ three contractions of the path through it:
   inverse   K^-1 = L^-T L^-1 (LAUUM) feeding the LML gradient   tolerance: gradient 1e-6 relative
   factor    every GEMM of the recursive Cholesky+inverse        tolerance: LML 1e-8 rel, L 1e-10 abs, alpha 1e-7 rel
 
-Splitting: row i of an operand is scaled by mu_i = 2^ceil(log2 max|a_i.|); slice 1 keeps 6 bits + sign, every
+Splitting: row i of an operand is scaled by mu_i = the power of two just above max|a_i.|; slice 1 keeps 6 bits + sign, every
 further slice 7 bits + sign (all fit int8); slice products with s + t <= S + 1 are kept (S(S+1)/2 products) and
 summed per s + t in one exact integer accumulator, then combined in float64 from the smallest scale up.
 
@@ -26,8 +26,9 @@ from scipy.spatial.distance import cdist
 def split(A, S):
     """rows of A -> (mu (rows,), [q_1..q_S] integer-valued float64 arrays, shifts[s] = bits kept through slice s)"""
     amax = np.max(np.abs(A), axis=1)
-    mu = np.where(amax > 0, 2.0 ** np.ceil(np.log2(np.where(amax > 0, amax, 1.0)) + 1e-12), 1.0)
-    r = A / mu[:, None]                       # |r| <= 1, exact (power of two)
+    _, e = np.frexp(amax)                     # amax = f * 2^e, f in [0.5, 1)  (csrc/gpk_i8gemm.cu does the same)
+    mu = np.where(amax > 0, np.ldexp(1.0, e), 1.0)
+    r = A / mu[:, None]                       # |r| < 1, exact (power of two)
     qs, shifts, bits = [], [], 0
     for s in range(S):
         b = 6 if s == 0 else 7
