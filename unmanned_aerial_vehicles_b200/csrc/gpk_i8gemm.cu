@@ -9,7 +9,11 @@
 //   C_ij = alpha * mu_i * nu_j * sum_{g=0}^{S-1} 2^-(12+7g) * P_g[i,j],   P_g = sum_{s+t=g} q^A_s (q^B_t)^T
 //
 // P_g is an exact integer: one int32 TMEM accumulator per g (64 columns each, S <= 8 -> <= 512 columns), fed by
-// tcgen05.mma.kind::i8 (M=128, N=64, K=32 per instruction) from TMA-staged, 64-byte-swizzled shared-memory tiles.
+// tcgen05.mma.kind::i8 from TMA-staged, swizzled shared-memory tiles.  The B slices of a stage lie back to back
+// ([t][64 rows][KB bytes]) and the accumulators lie back to back in tensor memory ([g][64 columns]), so for a fixed
+// A slice s the products with B slices t = 0..S-1-s -- which belong to accumulators g = s..S-1 -- are ONE wide
+// instruction: M=128, N=64*(S-s) (cut at N=256), K=32.  10 instructions per k-step at S=7 instead of 28, and the
+// A slice is read from shared memory once per wide instruction instead of once per product.
 // No intermediate drain: |P_g| <= (g+1) * K * 4096 < 2^31 for K <= 65536.
 //
 // CTA = one 128 x 64 tile of C, 256 threads: warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer,
@@ -18,20 +22,23 @@
 #include "gpk_common.cuh"
 #include "../../include/gpk.h"
 #include <cuda.h>
+#include <stdlib.h>
 
 #define I8_BM 128
 #define I8_BN 64
-#define I8_KB 64                 // int8 elements (= bytes) of K per pipeline stage: one 64-byte swizzle row
-#define I8_STAGES 2
+#define I8_KPAD 64               // planes are padded to multiples of this along K
 #define I8_MAXS 8
 #define I8_TMEM_COLS 512
-#define I8_A_SLICE_BYTES (I8_BM * I8_KB)     // 8192
-#define I8_B_SLICE_BYTES (I8_BN * I8_KB)     // 4096
+#define I8_SMEM_BUDGET (226 * 1024)   // dynamic shared memory the pipeline may use (227 KB per CTA minus statics)
+#define I8_MAX_STAGES 8
+// KB = int8 elements (= bytes) of K per pipeline stage = one swizzle row: 64 (SWIZZLE_64B, 2 k-steps per stage)
+// or 32 (SWIZZLE_32B, 1 k-step per stage, twice as many stages in the same shared memory)
 
 struct I8GemmParams {
   int S;                       // slices per operand (1..8)
+  int stages;                  // pipeline depth (host: as many as fit in I8_SMEM_BUDGET, <= I8_MAX_STAGES)
   int n_tiles;                 // tiles along N (grid.x = m_tiles * n_tiles)
-  int K;                       // padded K, multiple of I8_KB
+  int K;                       // padded K, multiple of I8_KPAD
   const double* mu_a;          // (M) power-of-two row scales of A
   const double* mu_b;          // (N) power-of-two row scales of B
   double* C; int ldc;          // GPK_EPI_STORE
@@ -87,57 +94,62 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, int (&v)[16]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// K-major operand tile, rows of 64 bytes, 64-byte swizzle: 8-row atoms of 512 bytes stacked along M/N.
-// Bit layout of the tcgen05 shared-memory matrix descriptor: start address >> 4 in [0,14), leading byte offset >> 4
-// in [16,30) (one atom along K: ignored, set to 1), stride byte offset >> 4 in [32,46) (512 B between 8-row groups),
-// version 1 in [46,48), base offset 0 (tiles are 512-byte aligned), layout type in [61,64): 4 = SWIZZLE_64B.
-__device__ __forceinline__ uint64_t smem_desc_k64(uint32_t addr) {
+// K-major operand tile, rows of KB bytes (KB = 64 or 32), swizzle width = KB: 8-row atoms of 8*KB bytes stacked
+// along M/N.  Bit layout of the tcgen05 shared-memory matrix descriptor: start address >> 4 in [0,14), leading byte
+// offset >> 4 in [16,30) (one atom along K: ignored, set to 1), stride byte offset >> 4 in [32,46) (8*KB bytes
+// between 8-row groups), version 1 in [46,48), base offset 0 (tiles are aligned to the swizzle repeat), layout type
+// in [61,64): 4 = SWIZZLE_64B, 6 = SWIZZLE_32B.
+template <int KB>
+__device__ __forceinline__ uint64_t smem_desc_kmajor(uint32_t addr) {
   uint64_t d = (uint64_t)((addr >> 4) & 0x3FFFu);
-  d |= (uint64_t)1 << 16;                                  // leading byte offset: not used by swizzled K-major layouts
-  d |= (uint64_t)((512u >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(((8u * KB) >> 4) & 0x3FFFu) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)4 << 61;
+  d |= (uint64_t)(KB == 64 ? 4 : 6) << 61;
   return d;
 }
 // instruction descriptor, kind::i8: D format S32 (2) at [4,6), A/B format signed 8-bit (1) at [7,10) / [10,13),
 // both operands K-major (bits 15, 16 = 0), N >> 3 at [17,23), M >> 4 at [24,29)
-__device__ __forceinline__ uint32_t idesc_i8_128x64() {
-  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(I8_BN >> 3) << 17) | ((uint32_t)(I8_BM >> 4) << 24);
+__device__ __forceinline__ uint32_t idesc_i8(int n) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(I8_BM >> 4) << 24);
 }
 
-// k-range of one tile after triangular trimming, in units of I8_KB blocks: [kb_lo, kb_hi)
+// k-range of one tile after triangular trimming, in units of KB-byte blocks: [kb_lo, kb_hi)
+template <int KB>
 __device__ __forceinline__ void tile_k_range(const I8GemmParams& p, int i0, int j0, int& kb_lo, int& kb_hi) {
   int lo = 0, hi = p.K;
   if (p.a_tri == GPK_TRI_LOWER) hi = min(hi, i0 + I8_BM);
   if (p.a_tri == GPK_TRI_UPPER) lo = max(lo, i0);
   if (p.b_tri == GPK_TRI_LOWER) hi = min(hi, j0 + I8_BN);
   if (p.b_tri == GPK_TRI_UPPER) lo = max(lo, j0);
-  kb_lo = lo / I8_KB;
-  kb_hi = (hi + I8_KB - 1) / I8_KB;
+  kb_lo = lo / KB;
+  kb_hi = (hi + KB - 1) / KB;
   if (kb_hi < kb_lo) kb_hi = kb_lo;
 }
 
 // ---------------------------------------------------------------------------------------------- GEMM kernel
+template <int KB>
 __global__ void __launch_bounds__(256, 1)
 gpk_i8_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                    const I8GemmParams p) {
+  constexpr uint32_t A_SLICE = I8_BM * KB, B_SLICE = I8_BN * KB;     // bytes of one slice tile in a stage
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[I8_STAGES], empty_bar[I8_STAGES], tmem_full_bar;
+  __shared__ __align__(8) uint64_t full_bar[I8_MAX_STAGES], empty_bar[I8_MAX_STAGES], tmem_full_bar;
   __shared__ uint32_t tmem_slot;
 
   const int tile_m = blockIdx.x / p.n_tiles, tile_n = blockIdx.x % p.n_tiles;
   const int i0 = tile_m * I8_BM, j0 = tile_n * I8_BN;
   if (p.lower_only && j0 >= i0 + I8_BM) return;            // whole CTA leaves before any barrier / TMEM state exists
   int kb_lo, kb_hi;
-  tile_k_range(p, i0, j0, kb_lo, kb_hi);
+  tile_k_range<KB>(p, i0, j0, kb_lo, kb_hi);
   const int num_kb = kb_hi - kb_lo;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int S = p.S;
-  const uint32_t stage_bytes = (uint32_t)S * (I8_A_SLICE_BYTES + I8_B_SLICE_BYTES);
-  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle atoms need 512-byte alignment
+  const int S = p.S, stages = p.stages;
+  const uint32_t stage_bytes = (uint32_t)S * (A_SLICE + B_SLICE);
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle atoms need (8*KB)-byte alignment
 
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < I8_STAGES; ++s) { mbar_init(smem_u32(&full_bar[s]), 1); mbar_init(smem_u32(&empty_bar[s]), 1); }
+    for (int s = 0; s < stages; ++s) { mbar_init(smem_u32(&full_bar[s]), 1); mbar_init(smem_u32(&empty_bar[s]), 1); }
     mbar_init(smem_u32(&tmem_full_bar), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -151,40 +163,43 @@ gpk_i8_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   const uint32_t tmem = tmem_slot;
 
   if (warp == 0 && lane == 0) {
-    // ---- TMA producer: one 3-D box per operand per stage = all S slices of a (rows x 64 B) tile
+    // ---- TMA producer: one 3-D box per operand per stage = all S slices of a (rows x KB bytes) tile
+    int st = 0;
+    uint32_t ph = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
-      const int st = kb % I8_STAGES;
-      const uint32_t ph = (uint32_t)(kb / I8_STAGES) & 1u;
       mbar_wait(smem_u32(&empty_bar[st]), ph ^ 1u);
       const uint32_t full = smem_u32(&full_bar[st]);
       mbar_expect_tx(full, stage_bytes);
       const uint32_t a_dst = tiles + (uint32_t)st * stage_bytes;
-      const uint32_t b_dst = a_dst + (uint32_t)S * I8_A_SLICE_BYTES;
-      tma_load_3d(a_dst, &tma_a, full, (kb_lo + kb) * I8_KB, i0, 0);
-      tma_load_3d(b_dst, &tma_b, full, (kb_lo + kb) * I8_KB, j0, 0);
+      const uint32_t b_dst = a_dst + (uint32_t)S * A_SLICE;
+      tma_load_3d(a_dst, &tma_a, full, (kb_lo + kb) * KB, i0, 0);
+      tma_load_3d(b_dst, &tma_b, full, (kb_lo + kb) * KB, j0, 0);
+      if (++st == stages) { st = 0; ph ^= 1u; }
     }
   } else if (warp == 1 && lane == 0) {
-    // ---- MMA issuer: per 32-byte k-step, S(S+1)/2 slice products, product (s, t) into accumulator g = s + t
-    const uint32_t idesc = idesc_i8_128x64();
+    // ---- MMA issuer.  Per 32-byte k-step and A slice s: B slices 0..S-1-s in one or two wide instructions
+    //      (N <= 256) into accumulator columns [64 s, 64 S).  s = 0 touches every column first, so it alone
+    //      carries the "overwrite" flag on the tile's first k-step.
+    int st = 0;
+    uint32_t ph = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
-      const int st = kb % I8_STAGES;
-      const uint32_t ph = (uint32_t)(kb / I8_STAGES) & 1u;
       mbar_wait(smem_u32(&full_bar[st]), ph);
       tc_fence_after();
       const uint32_t a_base = tiles + (uint32_t)st * stage_bytes;
-      const uint32_t b_base = a_base + (uint32_t)S * I8_A_SLICE_BYTES;
+      const uint32_t b_base = a_base + (uint32_t)S * A_SLICE;
 #pragma unroll
-      for (int kk = 0; kk < I8_KB / 32; ++kk) {
-        for (int g = 0; g < S; ++g) {
-          for (int s = 0; s <= g; ++s) {
-            const int t = g - s;
-            const uint64_t ad = smem_desc_k64(a_base + (uint32_t)s * I8_A_SLICE_BYTES + (uint32_t)kk * 32u);
-            const uint64_t bd = smem_desc_k64(b_base + (uint32_t)t * I8_B_SLICE_BYTES + (uint32_t)kk * 32u);
-            tc_mma_i8(tmem + (uint32_t)g * I8_BN, ad, bd, idesc, (kb | kk | s) != 0 ? 1u : 0u);
+      for (int kk = 0; kk < KB / 32; ++kk) {
+        for (int s = 0; s < S; ++s) {
+          const uint64_t ad = smem_desc_kmajor<KB>(a_base + (uint32_t)s * A_SLICE + (uint32_t)kk * 32u);
+          for (int t0 = 0; t0 < S - s; t0 += 4) {            // 4 slices of 64 rows = N 256
+            const int nt = min(4, S - s - t0);
+            const uint64_t bd = smem_desc_kmajor<KB>(b_base + (uint32_t)t0 * B_SLICE + (uint32_t)kk * 32u);
+            tc_mma_i8(tmem + (uint32_t)(s + t0) * I8_BN, ad, bd, idesc_i8(nt * I8_BN), (kb | kk | s) != 0 ? 1u : 0u);
           }
         }
       }
       tc_commit(smem_u32(&empty_bar[st]));                  // frees the stage once these MMAs have read it
+      if (++st == stages) { st = 0; ph ^= 1u; }
     }
     if (num_kb > 0) tc_commit(smem_u32(&tmem_full_bar));
   } else if (warp >= 4) {
@@ -312,18 +327,28 @@ static GpkEncodeTiledFn gpk_encode_tiled() {
   return fn;
 }
 
-// planes [S][rows][KP] int8 -> 3-D map (k, row, slice), box (64 B, box_rows, S), 64-byte swizzle
-static int make_plane_map(CUtensorMap* map, const int8_t* planes, int rows, int KP, int S, int box_rows) {
+// planes [S][rows][KP] int8 -> 3-D map (k, row, slice), box (KB bytes, box_rows, S), swizzle width = KB
+static int make_plane_map(CUtensorMap* map, const int8_t* planes, int rows, int KP, int S, int box_rows, int KB) {
   GpkEncodeTiledFn enc = gpk_encode_tiled();
   if (!enc) return -2000;
   cuuint64_t dims[3] = {(cuuint64_t)KP, (cuuint64_t)rows, (cuuint64_t)S};
   cuuint64_t strides[2] = {(cuuint64_t)KP, (cuuint64_t)rows * (cuuint64_t)KP};
-  cuuint32_t box[3] = {(cuuint32_t)I8_KB, (cuuint32_t)box_rows, (cuuint32_t)S};
+  cuuint32_t box[3] = {(cuuint32_t)KB, (cuuint32_t)box_rows, (cuuint32_t)S};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)planes, dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, KB == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -2000 - (int)r;
+}
+
+// stage width along K: 64 bytes (default) or 32 (GPK_I8_KB=32: half the stage, twice the pipeline depth)
+static int i8_stage_kb() {
+  static int kb = 0;
+  if (!kb) {
+    const char* e = getenv("GPK_I8_KB");
+    kb = (e && atoi(e) == 32) ? 32 : 64;
+  }
+  return kb;
 }
 
 extern "C" {
@@ -332,7 +357,7 @@ int gpk_i8_slice(const double* src_d, int ld, int rows, int K, int tri, int S, s
                  double* mu_d, void* stream) {
   if (!src_d || !planes_d || !mu_d) return -1;
   if (rows < 0 || K < 0 || ld < K || rowsP < rows || KP < K) return -2;
-  if (rowsP % I8_BN || KP % I8_KB) return -3;
+  if (rowsP % I8_BN || KP % I8_KPAD) return -3;
   if (S < 1 || S > I8_MAXS) return -6;
   if (rowsP == 0) return 0;
   gpk_i8_slice_kernel<<<rowsP, 256, 0, (cudaStream_t)stream>>>(src_d, ld, rows, K, tri, S, (int8_t*)planes_d, rowsP, KP, mu_d);
@@ -345,31 +370,38 @@ int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const s
                    int N, int KP, int S, double* C_d, int ldc, double alpha, int accumulate, int a_tri, int b_tri,
                    int lower_only, double* rowsq_d, void* stream) {
   if (!Aq_d || !mu_a_d || !Bq_d || !mu_b_d) return -1;
-  if (M <= 0 || N <= 0 || KP <= 0 || M % I8_BM || N % I8_BN || KP % I8_KB) return -3;
+  if (M <= 0 || N <= 0 || KP <= 0 || M % I8_BM || N % I8_BN || KP % I8_KPAD) return -3;
   if (S < 1 || S > I8_MAXS) return -8;
   if ((long long)S * KP * 4096 >= (1ll << 31)) return -7;          // int32 accumulators would overflow
   if (!C_d && !rowsq_d) return -9;
   if (lower_only && M != N) return -15;
   static bool attr_set[GPK_MAX_DEV] = {};
   const int dev = gpk_current_device();
-  const size_t smem = (size_t)I8_STAGES * S * (I8_A_SLICE_BYTES + I8_B_SLICE_BYTES) + 1024;
+  const int KB = i8_stage_kb();
+  const size_t stage_bytes = (size_t)S * (I8_BM + I8_BN) * KB;
+  int stages = (int)((I8_SMEM_BUDGET - 1024) / stage_bytes);
+  if (stages > I8_MAX_STAGES) stages = I8_MAX_STAGES;
+  if (stages < 2) return -8;
+  const size_t smem = (size_t)stages * stage_bytes + 1024;
   if (!attr_set[dev]) {
-    GPK_CHECK(cudaFuncSetAttribute(gpk_i8_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   I8_STAGES * I8_MAXS * (I8_A_SLICE_BYTES + I8_B_SLICE_BYTES) + 1024));
+    GPK_CHECK(cudaFuncSetAttribute(gpk_i8_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM_BUDGET));
+    GPK_CHECK(cudaFuncSetAttribute(gpk_i8_gemm_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM_BUDGET));
     attr_set[dev] = true;
   }
   CUtensorMap ma, mb;
-  int rc = make_plane_map(&ma, (const int8_t*)Aq_d, M, KP, S, I8_BM);
+  int rc = make_plane_map(&ma, (const int8_t*)Aq_d, M, KP, S, I8_BM, KB);
   if (rc) return rc;
-  rc = make_plane_map(&mb, (const int8_t*)Bq_d, N, KP, S, I8_BN);
+  rc = make_plane_map(&mb, (const int8_t*)Bq_d, N, KP, S, I8_BN, KB);
   if (rc) return rc;
   I8GemmParams p;
-  p.S = S; p.n_tiles = N / I8_BN; p.K = KP; p.mu_a = mu_a_d; p.mu_b = mu_b_d;
+  p.S = S; p.stages = stages; p.n_tiles = N / I8_BN; p.K = KP; p.mu_a = mu_a_d; p.mu_b = mu_b_d;
   p.C = C_d; p.ldc = ldc; p.alpha = alpha; p.accumulate = accumulate;
   p.a_tri = a_tri; p.b_tri = b_tri; p.lower_only = lower_only;
   p.epilogue = rowsq_d ? GPK_EPI_ROWSUMSQ : GPK_EPI_STORE;
   p.rowsq = rowsq_d; p.rowsq_ld = N / I8_BN;
-  gpk_i8_gemm_kernel<<<(M / I8_BM) * (N / I8_BN), 256, smem, (cudaStream_t)stream>>>(ma, mb, p);
+  const int grid = (M / I8_BM) * (N / I8_BN);
+  if (KB == 64) gpk_i8_gemm_kernel<64><<<grid, 256, smem, (cudaStream_t)stream>>>(ma, mb, p);
+  else          gpk_i8_gemm_kernel<32><<<grid, 256, smem, (cudaStream_t)stream>>>(ma, mb, p);
   GPK_LAUNCHED();
   GPK_CHECK(cudaGetLastError());
   return 0;
