@@ -73,6 +73,67 @@ def test_sliced_product_reaches_fp64_class_accuracy():
     assert errs[8] < errs[6] < errs[4]
 
 
+def kernel_model(A, B, S, a_tri=0, b_tri=0, lower_only=0, KB=64, alpha=1.0):
+    """Control flow of csrc/gpk_i8gemm.cu restated step by step -- tile loop, triangular k-range trimming, per k-step
+    one wide "instruction" per A slice over the stacked B slices (cut at N=256), the overwrite flag, accumulator
+    column ranges, epilogue order -- with NumPy standing in for the tensor pipe.  Keeps the kernel's logic honest
+    on the CPU; descriptors, swizzles and barriers are what only the GPU run can check."""
+    BM, BN = 128, 64
+    M, K = A.shape
+    N = B.shape[0]
+    assert M % BM == 0 and N % BN == 0 and K % 64 == 0
+    mua, qa, _ = split(A, S)
+    mub, qb, _ = split(B, S)
+    C = np.full((M, N), np.nan)
+    for i0 in range(0, M, BM):
+        for j0 in range(0, N, BN):
+            if lower_only and j0 >= i0 + BM:
+                continue
+            lo, hi = 0, K
+            if a_tri == 1: hi = min(hi, i0 + BM)
+            if a_tri == 2: lo = max(lo, i0)
+            if b_tri == 1: hi = min(hi, j0 + BN)
+            if b_tri == 2: lo = max(lo, j0)
+            kb_lo, kb_hi = lo // KB, max((hi + KB - 1) // KB, lo // KB)
+            tmem = np.full((BM, 64 * S), 12345.0)                      # stale tensor memory: must be overwritten
+            Bstack = np.concatenate([q[j0:j0 + BN] for q in qb], axis=0)   # [t][64 rows] back to back, like the stage
+            for kb in range(kb_lo, kb_hi):
+                for kk in range(KB // 32):
+                    k = kb * KB + kk * 32
+                    for s in range(S):
+                        a = qa[s][i0:i0 + BM, k:k + 32]
+                        for t0 in range(0, S - s, 4):
+                            nt = min(4, S - s - t0)
+                            d = a @ Bstack[t0 * 64:(t0 + nt) * 64, k:k + 32].T
+                            cols = slice((s + t0) * 64, (s + t0 + nt) * 64)
+                            first = (kb == kb_lo and kk == 0 and s == 0)
+                            tmem[:, cols] = d if first else tmem[:, cols] + d
+            acc = np.zeros((BM, BN))
+            if kb_hi > kb_lo:
+                for g in range(S - 1, -1, -1):
+                    acc += tmem[:, g * 64:(g + 1) * 64] * 2.0 ** -(12 + 7 * g)
+            C[i0:i0 + BM, j0:j0 + BN] = (acc * (alpha * mua[i0:i0 + BM])[:, None]) * mub[None, j0:j0 + BN]
+    return C
+
+
+@pytest.mark.parametrize("S,KB", [(1, 64), (4, 32), (7, 64), (7, 32), (8, 64)])
+def test_kernel_control_flow_model_matches_the_arithmetic(S, KB):
+    rng = np.random.default_rng(5)
+    A, B = _wide(rng, 256, 192), _wide(rng, 128, 192)
+    assert np.array_equal(kernel_model(A, B, S, KB=KB, alpha=-1.0), gemm_nt_sliced(A, B, S, alpha=-1.0))
+    n = 384
+    U = np.triu(rng.standard_normal((n, n)))
+    got = kernel_model(U, U, S, a_tri=2, b_tri=2, lower_only=1, KB=KB)          # LAUUM shape
+    want = gemm_nt_sliced(U, U, S)
+    low = np.tril_indices(n)
+    assert np.array_equal(got[low], want[low])
+    assert np.isnan(got[:128, 128:]).all()                                        # tiles above the diagonal untouched
+    Lo = np.tril(rng.standard_normal((n, n)))
+    Q = rng.standard_normal((128, n))
+    assert np.array_equal(kernel_model(Q, Lo, S, b_tri=1, KB=KB), gemm_nt_sliced(Q, Lo, S))   # predict shape
+    assert np.array_equal(kernel_model(Lo, Q, S, a_tri=1, KB=KB), gemm_nt_sliced(Lo, Q, S))
+
+
 # ------------------------------------------------------------------------------------------------ GPU (opt-in)
 _gated = pytest.mark.skipif(os.environ.get("GPK_I8_EXPERIMENT") != "1",
                             reason="experimental tcgen05 int8 path: set GPK_I8_EXPERIMENT=1 (never run on a GPU yet)")
