@@ -129,6 +129,7 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
                 "increasing the 'alpha' parameter of your GaussianProcessRegressor estimator.",
                 f"{info}-th leading minor of the array is not positive definite")
         self._low = low
+        self._yscale_b = (np.broadcast_to(self._y_train_mean, (eng.T,)), np.broadcast_to(self._y_train_std, (eng.T,)))
         a = eng.alpha_host()
         self.alpha_ = a if self.y_train_.ndim == 2 else a[:, 0]
         self.__dict__.pop("_L_cache", None)
@@ -152,7 +153,12 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
     def predict(self, X, return_std=False, return_cov=False):
         if return_std and return_cov:
             raise RuntimeError("At most one of return_std or return_cov can be requested.")
-        X = check_array(X, ensure_2d=True, dtype="numeric")
+        # the controller calls this 25 times per 20 ms tick with one float64 row (simple_gp.py:194, mpc.py:1490):
+        # a finite 2-D float64 ndarray is what check_array would hand back unchanged, so it skips the ~55 us of
+        # container sniffing; anything else takes the full validation and gets sklearn's own errors
+        if not (type(X) is np.ndarray and X.dtype == np.float64 and X.ndim == 2 and X.size
+                and np.isfinite(X).all()):
+            X = check_array(X, ensure_2d=True, dtype="numeric")
         if not hasattr(self, "X_train_"):  # prior (_gpr.py:417-443)
             kernel = C(1.0, constant_value_bounds="fixed") * RBF(1.0, length_scale_bounds="fixed") \
                 if self.kernel is None else self.kernel
@@ -173,8 +179,8 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         self._ensure_factored()
         eng = self._engine
         T = eng.T
-        mean, std, cov, nneg = eng.predict(X, np.broadcast_to(self._y_train_mean, (T,)),
-                                           np.broadcast_to(self._y_train_std, (T,)), return_std, return_cov)
+        scale = self._yscale_b                      # per-target mean/std, broadcast once in _finalize_factor
+        mean, std, cov, nneg = eng.predict(X, scale[0], scale[1], return_std, return_cov)
         y_mean = mean
         if self.y_train_.ndim == 1 or T == 1:
             y_mean = mean[:, 0]
@@ -240,6 +246,7 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         fitted = "X_train_" in state
         state.pop("_engine", None)
         state.pop("_low", None)
+        state.pop("_yscale_b", None)
         L = state.pop("_L_cache", None)
         if fitted:
             state["L_"] = L if L is not None else self.L_
