@@ -63,3 +63,24 @@ def test_prior_predict_needs_no_device():
     g = GaussianProcessRegressor(kernel=C(2.0) * RBF(1.0) + WhiteKernel(0.5))
     m, s = g.predict(np.zeros((4, 3)), return_std=True)
     assert m.shape == (4,) and np.allclose(s, np.sqrt(2.5))
+
+
+@pytest.mark.parametrize("k,d", [
+    (RBF(0.5) + WhiteKernel(0.1), 10),                                                   # simple_gp.py:167
+    (C(1.0, constant_value_bounds="fixed") * RBF([1.0] * 9, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0)), 9),
+    (WhiteKernel(0.05) + C(2.0) * RBF([1.5, 0.7, 3.0]), 3),
+    (RBF([1.0, 2.0], length_scale_bounds="fixed") + WhiteKernel(0.3), 2),               # fixed length-scales
+    (C(2.0) * RBF(1.5), 4),
+])
+def test_with_theta_equals_lowering_the_cloned_kernel(k, d):
+    """the optimiser's shortcut (theta -> flat parameters) gives bit for bit what sklearn's theta setter gives"""
+    rng = np.random.default_rng(0)
+    template = lower(k, d)
+    for _ in range(20):
+        theta = k.theta + rng.uniform(-3, 3, size=k.theta.shape)
+        fast, slow = template.with_theta(theta), lower(k.clone_with_theta(theta), d)
+        assert fast.c == slow.c and fast.noise == slow.noise and fast.iso == slow.iso
+        assert np.array_equal(fast.length_scale, slow.length_scale) and fast.theta_map == slow.theta_map
+    assert np.array_equal(template.length_scale, lower(k, d).length_scale)               # template untouched
+    with pytest.raises(ValueError):
+        template.with_theta(np.zeros(len(k.theta) + 1))

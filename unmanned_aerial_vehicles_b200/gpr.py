@@ -86,14 +86,20 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         self.y_train_ = np.copy(y) if self.copy_X_train else y
         self._engine = None
         self._low = None
-        lower(self.kernel_, X.shape[1])  # raises early for unsupported kernels
+        template = lower(self.kernel_, X.shape[1])  # raises early for unsupported kernels
 
         if self.optimizer is not None and self.kernel_.n_dims > 0:
             def obj_func(theta, eval_gradient=True):
-                if eval_gradient:
-                    lml, grad = self.log_marginal_likelihood(theta, eval_gradient=True, clone_kernel=False)
-                    return -lml, -grad
-                return -self.log_marginal_likelihood(theta, clone_kernel=False)
+                # _gpr.py:302-310 with clone_kernel=False, minus the per-evaluation walk over sklearn's kernel
+                # objects: theta goes straight to the flat parameter set (kernel_.theta is set once, at the end)
+                low = template.with_theta(theta)
+                lml, g_c, g_ls, g_noise = self._engine_for_training().lml(
+                    1.0 / low.length_scale, low.c, low.noise, eval_gradient)
+                if not eval_gradient:
+                    return -lml
+                if not np.isfinite(lml):
+                    return np.inf, np.zeros(len(low.theta_map))
+                return -lml, -assemble_gradient(low, g_c, g_ls, g_noise)
 
             # starting points exactly as sklearn draws them (_gpr.py:312-333): kernel theta, then log-uniform
             starts = [self.kernel_.theta]

@@ -26,6 +26,25 @@ class Lowered:
     # one entry per element of theta: ("c",0) | ("ls",d) | ("ls_iso",0) | ("noise",0)
     theta_map: list
 
+    def with_theta(self, theta) -> "Lowered":
+        """Same kernel structure at another theta (log space, sklearn's order) without touching sklearn's kernel
+        objects: what ``lower(kernel.clone_with_theta(theta), D)`` returns, at a fraction of its host cost (the
+        optimiser calls this once per objective evaluation; sklearn's theta setter walks ``dir()`` of every node)."""
+        v = np.exp(np.asarray(theta, dtype=np.float64))
+        if v.shape != (len(self.theta_map),):
+            raise ValueError(f"theta has shape {v.shape}, kernel has {len(self.theta_map)} free hyper-parameters")
+        c, noise, ls = self.c, self.noise, self.length_scale.copy()
+        for k, (kind, d) in enumerate(self.theta_map):
+            if kind == "c":
+                c = float(v[k])
+            elif kind == "noise":
+                noise = float(v[k])
+            elif kind == "ls":
+                ls[d] = v[k]
+            else:
+                ls[:] = v[k]
+        return Lowered(c=c, length_scale=ls, noise=noise, iso=self.iso, theta_map=self.theta_map)
+
 
 def _split(kernel):
     """-> (const_kernel|None, rbf, white|None) or raise."""
