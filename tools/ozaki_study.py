@@ -164,10 +164,21 @@ def case(name, X, Y, ls, c, noise, jitter, Xq, slices):
         Vt = g(ref["Ks"], Mt)
         std_t = np.sqrt(np.maximum((c + noise) - np.sum(Vt * Vt, axis=1), 0.0))
         assert np.array_equal(Lt, ref["L"])
+        # alpha through the tail-emulated M, then one refinement step over the FP64 factor:
+        #   r = y - L (L^T a0),  a = a0 + M^T (M r)
+        a0 = Mt.T @ (Mt @ Y)
+        a1 = a0 + Mt.T @ (Mt @ (Y - Lt @ (Lt.T @ a0)))
+        amax = np.max(np.abs(ref["alpha"]))
+        lml_of = lambda al: float(np.sum(-0.5 * np.einsum("ik,ik->k", Y, al)) - Y.shape[1] * np.log(np.diag(Lt)).sum()
+                                  - Y.shape[1] * N / 2 * np.log(2 * np.pi))
         row = {
             "case": name, "N": N, "slices": S, "products": S * (S + 1) // 2,
             "tail_lauum_grad_rel": rel(grad_t, ref["grad"]),
             "tail_lauum_predict_std_abs": float(np.max(np.abs(std_t - ref["std"]))),
+            "tail_alpha_rel": float(np.max(np.abs(a0 - ref["alpha"])) / amax),
+            "tail_alpha_refined_rel": float(np.max(np.abs(a1 - ref["alpha"])) / amax),
+            "tail_lml_rel": abs(lml_of(a0) - ref["lml"]) / abs(ref["lml"]),
+            "tail_lml_refined_rel": abs(lml_of(a1) - ref["lml"]) / abs(ref["lml"]),
             "inv_lauum_L_abs": float(np.max(np.abs(Lm - ref["L"]))),
             "inv_lauum_alpha_rel": float(np.max(np.abs(am - ref["alpha"])) / np.max(np.abs(ref["alpha"]))),
             "inv_lauum_lml_rel": abs(lml_m - ref["lml"]) / abs(ref["lml"]),
