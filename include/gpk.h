@@ -107,7 +107,7 @@ int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pa
 /* *sum_d += sum_i log A[i,i], i < n */
 int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
 
-/* EXPERIMENTAL (not called by the estimator yet): FP64-accurate C = alpha * A * B^T on the tcgen05
+/* EXPERIMENTAL (off unless GPK_I8 is set, see below): FP64-accurate C = alpha * A * B^T on the tcgen05
  * INT8 pipe.  Operands are pre-split into S int8 slice planes with one power-of-two scale per row:
  *   a[i,k] = mu[i] * sum_s planes[s][i][k] * 2^-(6+7s),   |planes| <= 64,   planes laid out [S][rowsP][KP], K contiguous.
  * gpk_i8_slice: src_d (rows x K, leading dimension ld; tri = 0 full, 1 lower, 2 upper: only that triangle is read)
@@ -122,6 +122,18 @@ int gpk_i8_slice(const double* src_d, int ld, int rows, int K, int tri, int S, s
 int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const signed char* Bq_d, const double* mu_b_d,
                    int N, int KP, int S, double* C_d, int ldc, double alpha, int accumulate, int a_tri, int b_tri,
                    int lower_only, double* rowsq_d, void* stream);
+/* EXPERIMENTAL opt-in use of the two calls above on the estimator's path (engine.py does this only when the
+ * environment sets GPK_I8; default: never).  gpk_i8_configure registers caller-owned device scratch of at least
+ * gpk_i8_workspace_bytes(NP, MPmax, S) bytes for the current device; mode bit 1: gpk_lml_eval forms K^-1 = L^-T L^-1
+ * from int8 planes of L^-T; bit 2: gpk_predict / gpk_predict_std form the variance contraction Ks L^-T from planes of
+ * L^-1 that gpk_i8_prepare_predict(Mlow_d) sliced after the final factorisation (any later gpk_potrf_inv /
+ * gpk_lml_eval drops them).  Shapes the int8 kernel cannot take (NP or the padded query rows not a multiple of 128,
+ * more query rows than MPmax) silently use the FP64 DMMA kernel.  ws_d = NULL or mode = 0 switches it off.
+ * gpk_i8_workspace_bytes returns 0 for an unsupported shape; gpk_i8_mode returns the active mode bits. */
+size_t gpk_i8_workspace_bytes(int NP, int MPmax, int S);
+int gpk_i8_configure(void* ws_d, size_t bytes, int NP, int MPmax, int S, int mode);
+int gpk_i8_prepare_predict(const double* Mlow_d, int NP, void* stream);
+int gpk_i8_mode(void);
 
 /* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
  * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */

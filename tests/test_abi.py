@@ -47,3 +47,19 @@ def test_no_cpu_fallback_without_cuda():
     g = GaussianProcessRegressor(kernel=RBF(1.0), optimizer=None)
     with pytest.raises(GpkUnavailable):
         g.fit(np.random.rand(10, 2), np.random.rand(10))
+
+
+def test_int8_opt_in_registration_is_pure_host_and_off_by_default():
+    lib = _lib.load()
+    assert lib.gpk_i8_mode() == 0                                             # nothing enabled unless asked
+    al = lambda b: (b + 255) & ~255
+    NP, MP, S = 20096, 16384, 7
+    want = 2 * (al(S * NP * NP) + al(8 * NP)) + al(S * MP * NP) + al(8 * MP)
+    assert lib.gpk_i8_workspace_bytes(NP, MP, S) == want
+    assert lib.gpk_i8_workspace_bytes(NP + 64, MP, S) == 0                    # NP must be a multiple of 128
+    assert lib.gpk_i8_workspace_bytes(NP, MP, 9) == 0                         # at most 8 slices (512 TMEM columns)
+    fake = ctypes.c_void_p(0x1000)                                            # never dereferenced by configure
+    assert lib.gpk_i8_configure(fake, want - 1, NP, MP, S, 3) == -2 and lib.gpk_i8_mode() == 0
+    assert lib.gpk_i8_configure(fake, want, NP, MP, 8, 3) != 0 and lib.gpk_i8_mode() == 0
+    assert lib.gpk_i8_configure(fake, want, NP, MP, S, 3) == 0 and lib.gpk_i8_mode() == 3
+    assert lib.gpk_i8_configure(None, 0, 0, 0, 0, 0) == 0 and lib.gpk_i8_mode() == 0

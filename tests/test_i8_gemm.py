@@ -5,7 +5,7 @@ for bit -- reconstructs its input to the promised number of bits and gives FP64-
 
 GPU part: written in round 1 after the GPU budget was spent, so the kernels have compiled but never run.  It is
 therefore opt-in (GPK_I8_EXPERIMENT=1) until its first green run on a B200; the default GPU suite does not depend
-on it and nothing on the estimator's path calls these entry points yet.
+on it and the estimator's path reaches these entry points only when GPK_I8 is set (last test below).
 """
 import os
 
@@ -233,3 +233,47 @@ def test_device_triangular_trimming_and_lower_only():
                             V.data_ptr(), NP, 1.0, 0, 0, 1, 0, None, st)
     assert rc == 0, rc
     assert np.array_equal(V.cpu().numpy()[:256, :n], gemm_nt_sliced(Q, Lo, S))
+
+
+def _path_case(n=1000, d=9, t=3, seed=5):
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((n, d))
+    Y = np.sin(X @ (rng.standard_normal((d, t)) / np.sqrt(d))) + 0.1 * rng.standard_normal((n, t))
+    return X, Y, rng.standard_normal((2048, d))
+
+
+@pytest.mark.gpu
+@_gated
+@pytest.mark.parametrize("theta_shift", [0.0, -1.5])
+def test_estimator_path_with_int8_lauum_and_predict(monkeypatch, theta_shift):
+    """GPK_I8=3 routes K^-1 (objective gradient) and predict's variance contraction through the int8 kernel; the
+    FP64 DMMA run of the same estimator is the yardstick (tolerances from tools/ozaki_study.py at 7 slices)."""
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+    from unmanned_aerial_vehicles_b200 import GaussianProcessRegressor, _lib
+    X, Y, Xq = _path_case()
+    k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 9, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0))
+
+    def run():
+        g = GaussianProcessRegressor(kernel=k, alpha=1e-6, optimizer=None).fit(X, Y)
+        th = g.kernel_.theta + theta_shift
+        lml, grad = g.log_marginal_likelihood(th, eval_gradient=True)
+        m, s = g.predict(Xq, return_std=True)
+        m1, s1 = g.predict(Xq[:3], return_std=True)          # small-batch kernel: FP64 in both runs
+        return lml, grad, m, s, m1, s1, g
+
+    monkeypatch.delenv("GPK_I8", raising=False)
+    lml0, grad0, m0, s0, m10, s10, g0 = run()
+    assert g0._engine.i8_mode == 0 and _lib.load().gpk_i8_mode() == 0
+    monkeypatch.setenv("GPK_I8", "3")
+    lml1, grad1, m1, s1, m11, s11, g1 = run()
+    assert g1._engine.i8_mode == 3 and _lib.load().gpk_i8_mode() == 3
+    assert lml1 == lml0 and np.array_equal(m1, m0)           # factor, alpha and mean never leave FP64
+    np.testing.assert_allclose(grad1, grad0, rtol=1e-8, atol=1e-8 * np.abs(grad0).max())
+    np.testing.assert_allclose(s1, s0, rtol=0, atol=1e-9)
+    assert np.array_equal(m11, m10) and np.array_equal(s11, s10)
+    # libgpk holds one scratch per device: an engine built without the opt-in switches it off for its own calls,
+    # the opt-in engine re-registers (and re-slices L^-1) on its next one
+    np.testing.assert_array_equal(g0.predict(Xq, return_std=True)[1], s0)
+    assert _lib.load().gpk_i8_mode() == 0
+    np.testing.assert_array_equal(g1.predict(Xq, return_std=True)[1], s1)
+    assert _lib.load().gpk_i8_mode() == 3

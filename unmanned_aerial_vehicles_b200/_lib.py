@@ -17,7 +17,7 @@ SYMBOLS = (
     "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
     "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
     "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_leaf_phase_cycles", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
-    "gpk_i8_slice", "gpk_i8_gemm_nt",
+    "gpk_i8_slice", "gpk_i8_gemm_nt", "gpk_i8_workspace_bytes", "gpk_i8_configure", "gpk_i8_prepare_predict", "gpk_i8_mode",
 )
 
 
@@ -65,12 +65,18 @@ def _declare(lib):
     lib.gpk_leaf_phase_cycles.argtypes = [_p]
     lib.gpk_i8_slice.argtypes = [_p, _i, _i, _i, _i, _i, _p, _i, _i, _p, _p]
     lib.gpk_i8_gemm_nt.argtypes = [_p, _p, _i, _p, _p, _i, _i, _i, _p, _i, _d, _i, _i, _i, _i, _p, _p]
+    lib.gpk_i8_workspace_bytes.argtypes = [_i, _i, _i]
+    lib.gpk_i8_workspace_bytes.restype = C.c_size_t
+    lib.gpk_i8_configure.argtypes = [_p, C.c_size_t, _i, _i, _i, _i]
+    lib.gpk_i8_prepare_predict.argtypes = [_p, _i, _p]
+    lib.gpk_i8_mode.argtypes = []
     lib.gpk_launch_count.restype = C.c_ulonglong
     lib.gpk_profile_launch.argtypes = [_i, _dp, _dp, C.POINTER(C.c_int)]
     lib.gpk_profile_end.argtypes = [_dp, _dp, C.POINTER(C.c_int)]
     for name in SYMBOLS:
         fn = getattr(lib, name)
-        if name not in ("gpk_grad_workspace_doubles", "gpk_launch_count"):
+        if name not in ("gpk_grad_workspace_doubles", "gpk_predict_workspace_doubles", "gpk_i8_workspace_bytes",
+                        "gpk_launch_count"):
             fn.restype = _i
 
 

@@ -66,6 +66,7 @@ int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, 
 int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream) {
   if (!A_d) return -1; if (!Mlow_d) return -2; if (!Mup_d) return -3; if (NP < GPK_TILE || NP % GPK_TILE) return -4;
   if (!info_d) return -5;
+  gpk_i8_invalidate();
   GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, (cudaStream_t)stream));
   return 0;
 }
@@ -106,12 +107,18 @@ int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double
   if (NP != gpk_pad(N)) return -15;
   const size_t nt = (size_t)NP / 64;
   double* diag = ws_d + nt * nt * (size_t)(gpk_dp_of(D) + 2);
+  gpk_i8_invalidate();
   GPK_CHECK(gpk_launch_gram(X_d, N, D, p, A_d, NP, 1, st));
   GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st));
   GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, st));
   GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, st));
   GPK_CHECK(gpk_launch_copy_diag(A_d, NP, NP, diag, st));
-  if (with_grad) GPK_CHECK(gpk_launch_lauum(Mup_d, NP, A_d, NP, NP, st));
+  if (with_grad) {
+    // opt-in (gpk_i8_configure, mode bit 1): K^-1 from int8 slice planes on the tcgen05 pipe; 0 = not taken
+    const int took = gpk_i8_mode() ? gpk_i8_try_lauum(Mup_d, NP, A_d, NP, NP, st) : 0;
+    if (took < 0) return took;
+    if (!took) GPK_CHECK(gpk_launch_lauum(Mup_d, NP, A_d, NP, NP, st));
+  }
   p.jitter = 0.0;
   GPK_CHECK(gpk_launch_lml_grad(X_d, N, D, p, diag, 1, y_d, alpha_d, T, A_d, NP, with_grad, ws_d, out_d, st));
   return 0;
@@ -141,10 +148,14 @@ int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, in
     GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / 32, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
     return 0;
   }
-  GpkGemmArgs g{};
-  g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
-  g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
-  GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
+  const int took = gpk_i8_mode() ? gpk_i8_try_predict_rowsq(Ks_d, MP, Mlow_d, NP, rowsq_d, (cudaStream_t)stream) : 0;
+  if (took < 0) return took;
+  if (!took) {
+    GpkGemmArgs g{};
+    g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+    g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
+    GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
+  }
   GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_ROWSQ_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
   return 0;
 }
@@ -183,10 +194,14 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
       GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks, Mq, rowsq, st));
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / 32, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     } else {
-      GpkGemmArgs g{};
-      g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
-      g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
-      GPK_CHECK(gpk_launch_gemm_nt(g, st));
+      const int took = gpk_i8_mode() ? gpk_i8_try_predict_rowsq(Ks, MP, Mlow_d, NP, rowsq, st) : 0;
+      if (took < 0) return took;
+      if (!took) {
+        GpkGemmArgs g{};
+        g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+        g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
+        GPK_CHECK(gpk_launch_gemm_nt(g, st));
+      }
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_ROWSQ_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     }
     GPK_CHECK(cudaMemcpyAsync(std_h, std_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));

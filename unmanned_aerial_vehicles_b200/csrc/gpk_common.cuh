@@ -52,6 +52,13 @@ cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, 
 #define GPK_MAX_DEV 64
 static inline int gpk_current_device() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < GPK_MAX_DEV) ? d : 0; }
 
+// opt-in int8 (tcgen05) contraction, gpk_i8gemm.cu: per-device registered scratch and what it may be used for
+struct GpkI8State { char* ws; size_t bytes; int NP, MPmax, S, mode; const double* prepared; };
+extern "C" int gpk_i8_mode();            // 0 unless gpk_i8_configure() enabled something on the current device
+extern "C" void gpk_i8_invalidate();     // the L^-1 whose planes were prepared for predict is about to change
+int gpk_i8_try_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, cudaStream_t st);
+int gpk_i8_try_predict_rowsq(const double* Ks, int MP, const double* Mlow, int NP, double* rowsq, cudaStream_t st);
+
 extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)
 #define GPK_LAUNCHED() (++g_gpk_launches)
 // optional per-launch timing of the DMMA GEMM (bench.py roofline): event pairs around each launch

@@ -1,4 +1,4 @@
-// gpk_i8gemm.cu -- EXPERIMENTAL, not on the default path (nothing in engine.py calls it yet).
+// gpk_i8gemm.cu -- EXPERIMENTAL, not on the default path (engine.py registers scratch for it only when GPK_I8 is set).
 //
 // FP64-accurate NT GEMM on the tcgen05 INT8 pipe (Ozaki splitting): C = alpha * A * B^T with A (M x K), B (N x K)
 // given as S int8 "slice planes" per operand plus one power-of-two scale per row (gpk_i8_slice produces them).
@@ -407,4 +407,78 @@ int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const s
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------- opt-in use on the path
+// Nothing below runs unless gpk_i8_configure() has registered scratch on the current device (engine.py does that
+// only when GPK_I8 is set).  mode bit 1: K^-1 = L^-T L^-1 (LAUUM) of gpk_lml_eval; bit 2: predict's Ks L^-T.
+static GpkI8State g_i8[GPK_MAX_DEV];
+
+static inline size_t i8_align(size_t b) { return (b + 255) & ~(size_t)255; }
+static inline size_t i8_square_bytes(int NP, int S) { return i8_align((size_t)S * NP * NP) + i8_align(sizeof(double) * (size_t)NP); }
+static inline size_t i8_rows_bytes(int MP, int NP, int S) { return i8_align((size_t)S * MP * NP) + i8_align(sizeof(double) * (size_t)MP); }
+
+size_t gpk_i8_workspace_bytes(int NP, int MPmax, int S) {
+  if (NP < I8_BM || NP % I8_BM || MPmax < 0 || MPmax % I8_BM || S < 1 || S > I8_MAXS) return 0;
+  return 2 * i8_square_bytes(NP, S) + i8_rows_bytes(MPmax, NP, S);
+}
+
+int gpk_i8_configure(void* ws_d, size_t bytes, int NP, int MPmax, int S, int mode) {
+  GpkI8State& g = g_i8[gpk_current_device()];
+  g = GpkI8State{};
+  if (!ws_d || mode == 0) return 0;                              // disabled
+  const size_t need = gpk_i8_workspace_bytes(NP, MPmax, S);
+  if (need == 0) return -3;
+  if (bytes < need) return -2;
+  if ((long long)S * NP * 4096 >= (1ll << 31)) return -7;
+  g.ws = (char*)ws_d; g.bytes = bytes; g.NP = NP; g.MPmax = MPmax; g.S = S; g.mode = mode;
+  return 0;
+}
+
+int gpk_i8_mode() { return g_i8[gpk_current_device()].mode; }
+
+void gpk_i8_invalidate() { g_i8[gpk_current_device()].prepared = nullptr; }
+
+int gpk_i8_prepare_predict(const double* Mlow_d, int NP, void* stream) {
+  GpkI8State& g = g_i8[gpk_current_device()];
+  g.prepared = nullptr;
+  if (!(g.mode & 2)) return 0;
+  if (!Mlow_d) return -1;
+  if (NP != g.NP) return -2;
+  signed char* planes = (signed char*)g.ws;
+  double* mu = (double*)(g.ws + i8_align((size_t)g.S * NP * NP));
+  int rc = gpk_i8_slice(Mlow_d, NP, NP, NP, GPK_TRI_LOWER, g.S, planes, NP, NP, mu, stream);
+  if (rc) return rc;
+  g.prepared = Mlow_d;
+  return 0;
+}
+
 }  // extern "C"
+
+// K^-1 (lower tiles) = Mup Mup^T from the int8 planes of Mup = L^-T.  Returns 1 when it did the work, 0 when the
+// int8 path is not configured for this shape (caller falls through to the DMMA kernel), < 0 on error.
+int gpk_i8_try_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, cudaStream_t st) {
+  GpkI8State& g = g_i8[gpk_current_device()];
+  if (!(g.mode & 1) || NP != g.NP || ldm != NP) return 0;
+  char* base = g.ws + i8_square_bytes(NP, g.S);                  // second square region (the first holds predict's L^-1)
+  signed char* planes = (signed char*)base;
+  double* mu = (double*)(base + i8_align((size_t)g.S * NP * NP));
+  int rc = gpk_i8_slice(Mup, ldm, NP, NP, GPK_TRI_UPPER, g.S, planes, NP, NP, mu, st);
+  if (rc) return rc;
+  rc = gpk_i8_gemm_nt(planes, mu, NP, planes, mu, NP, NP, g.S, Kinv, ldk, 1.0, 0, GPK_TRI_UPPER, GPK_TRI_UPPER, 1, nullptr, st);
+  return rc ? rc : 1;
+}
+
+// rowsq (MP x NP/64) = per-tile row sums of squares of Ks L^-T through the prepared planes of L^-1.  Same return
+// convention as gpk_i8_try_lauum.
+int gpk_i8_try_predict_rowsq(const double* Ks, int MP, const double* Mlow, int NP, double* rowsq, cudaStream_t st) {
+  GpkI8State& g = g_i8[gpk_current_device()];
+  if (!(g.mode & 2) || g.prepared != Mlow || NP != g.NP || MP > g.MPmax || MP % I8_BM) return 0;
+  const signed char* lp = (const signed char*)g.ws;
+  const double* lmu = (const double*)(g.ws + i8_align((size_t)g.S * NP * NP));
+  char* base = g.ws + 2 * i8_square_bytes(NP, g.S);
+  signed char* kp = (signed char*)base;
+  double* kmu = (double*)(base + i8_align((size_t)g.S * MP * NP));
+  int rc = gpk_i8_slice(Ks, NP, MP, NP, GPK_TRI_NONE, g.S, kp, MP, NP, kmu, st);
+  if (rc) return rc;
+  rc = gpk_i8_gemm_nt(kp, kmu, MP, lp, lmu, NP, NP, g.S, nullptr, 0, 1.0, 0, GPK_TRI_NONE, GPK_TRI_LOWER, 0, rowsq, st);
+  return rc ? rc : 1;
+}

@@ -7,6 +7,7 @@ through the C ABI (include/gpk.h).  Mirrors the arithmetic of sklearn/gaussian_p
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 
 import numpy as np
@@ -20,6 +21,9 @@ def _torch_cuda():
     if not torch.cuda.is_available():
         raise _lib.GpkUnavailable("no CUDA device: the GP hot path has no CPU fallback")
     return torch
+
+
+_I8_OWNER = {}   # device index -> (id(engine), scratch pointer) whose int8 scratch libgpk currently holds
 
 
 class DeviceGP:
@@ -68,6 +72,49 @@ class DeviceGP:
             self.A_d = t.empty(shape, dtype=t.float64, device=self.device)
             self.Mlow_d = t.empty(shape, dtype=t.float64, device=self.device)
             self.Mup_d = t.empty(shape, dtype=t.float64, device=self.device)
+            self._configure_i8()
+
+    def _configure_i8(self):
+        """EXPERIMENTAL, off unless GPK_I8 is set (bit 1: K^-1 of the objective, bit 2: predict's variance
+        contraction; GPK_I8_SLICES, default 7): allocates the scratch libgpk's int8-sliced tcgen05 contraction needs
+        (DESIGN.md section 8).  A shape it cannot take is an error here, not a silent fall back."""
+        self.i8_mode = 0
+        self._i8_planes_ok = False
+        mode = int(os.environ.get("GPK_I8", "0") or 0)
+        if mode == 0:
+            return
+        t = self.torch
+        S = int(os.environ.get("GPK_I8_SLICES", "7"))
+        MPmax = self._chunk_rows_default()
+        nbytes = int(self.lib.gpk_i8_workspace_bytes(self.NP, MPmax, S))
+        if nbytes == 0:
+            raise _lib.GpkError(f"GPK_I8: unsupported shape NP={self.NP} MPmax={MPmax} S={S}")
+        self._i8_ws = t.empty(nbytes, dtype=t.uint8, device=self.device)
+        self._i8_cfg = (nbytes, self.NP, MPmax, S, mode)
+        self.i8_mode = mode
+
+    def _i8_bind(self, need_planes: bool = False):
+        """libgpk keeps ONE registered int8 scratch per device; several engines can live on a device (one per
+        output in PerOutputGP), so each call re-registers its own when another engine's is in place, and predict
+        re-slices L^-1 when its planes were lost that way.  Call inside ``torch.cuda.device(self.device)``."""
+        dev = self.device.index
+        if not getattr(self, "i8_mode", 0):
+            if _I8_OWNER.get(dev) is not None:       # another engine's opt-in must not leak into this one
+                _lib.check(self.lib.gpk_i8_configure(None, 0, 0, 0, 0, 0), "gpk_i8_configure")
+                _I8_OWNER[dev] = None
+            return
+        me = (id(self), self._i8_ws.data_ptr())
+        if _I8_OWNER.get(dev) != me:
+            _lib.check(self.lib.gpk_i8_configure(self._p(self._i8_ws), *self._i8_cfg), "gpk_i8_configure")
+            _I8_OWNER[dev] = me
+            self._i8_planes_ok = False
+        if need_planes and (self.i8_mode & 2) and not self._i8_planes_ok:
+            _lib.check(self.lib.gpk_i8_prepare_predict(self._p(self.Mlow_d), self.NP, self._stream()),
+                       "gpk_i8_prepare_predict")
+            self._i8_planes_ok = True
+
+    def _chunk_rows_default(self) -> int:
+        return int(min(16384, max(128, (2 << 30) // (self.NP * 8)))) // 128 * 128
 
     @staticmethod
     def _p(t):
@@ -80,6 +127,8 @@ class DeviceGP:
         t = self.torch
         self._bufs()
         with t.cuda.device(self.device):
+            self._i8_bind()
+            self._i8_planes_ok = False
             rc = self.lib.gpk_lml_eval(
                 self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter, self._p(self.y_d), self.T,
                 self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self._p(self.u_d), self._p(self.alpha_d),
@@ -105,6 +154,8 @@ class DeviceGP:
         key = (tuple(float(v) for v in inv_ls), float(c), float(noise))
         with t.cuda.device(self.device):
             st = self._stream()
+            self._i8_bind()
+            self._i8_planes_ok = False
             _lib.check(self.lib.gpk_gram(self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter,
                                          self._p(self.A_d), self.NP, 1, st), "gpk_gram")
             _lib.check(self.lib.gpk_potrf_inv(self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self.NP,
@@ -112,6 +163,8 @@ class DeviceGP:
             _lib.check(self.lib.gpk_potrs(self._p(self.Mlow_d), self._p(self.Mup_d), self.NP, self._p(self.y_d),
                                           self._p(self.u_d), self._p(self.alpha_d), self.T, st), "gpk_potrs")
             info = int(self.info_d[:1].cpu()[0])
+            if info == 0:
+                self._i8_bind(need_planes=True)
         self.factored = key if info == 0 else None
         self.a_holds_L = info == 0
         return info
@@ -171,7 +224,7 @@ class DeviceGP:
         M = Xq.shape[0]
         NP, T = self.NP, self.T
         if chunk_rows is None:
-            chunk_rows = int(min(16384, max(128, (2 << 30) // (NP * 8))))
+            chunk_rows = self._chunk_rows_default()
         chunk_rows = max(128, (chunk_rows // 128) * 128)
         if return_cov:
             chunk_rows = ((M + 127) // 128) * 128
@@ -183,6 +236,7 @@ class DeviceGP:
             st = self._stream()
             ym, ys = self._target_scale(y_mean, y_std)
             inv_h = _lib.darr(inv_ls)
+            self._i8_bind(need_planes=True)
             if not return_cov:
                 MPmax, ws_d, ws_n, neg_h = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128))
                 for s in range(0, M, chunk_rows):
