@@ -127,7 +127,8 @@ int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const s
  * gpk_i8_workspace_bytes(NP, MPmax, S) bytes for the current device; mode bit 1: gpk_lml_eval forms K^-1 = L^-T L^-1
  * from int8 planes of L^-T; bit 2: gpk_predict / gpk_predict_std form the variance contraction Ks L^-T from planes of
  * L^-1 that gpk_i8_prepare_predict(Mlow_d) sliced after the final factorisation (any later gpk_potrf_inv /
- * gpk_lml_eval drops them).  Shapes the int8 kernel cannot take (NP or the padded query rows not a multiple of 128,
+ * gpk_lml_eval drops them); bit 4: gpk_lml_eval (never gpk_potrf_inv) forms the inverse blocks that no later panel
+ * of the factorisation reads -- those of the right-most path of its recursion -- from int8 planes as well.  Shapes the int8 kernel cannot take (NP or the padded query rows not a multiple of 128,
  * more query rows than MPmax) silently use the FP64 DMMA kernel.  ws_d = NULL or mode = 0 switches it off.
  * gpk_i8_workspace_bytes returns 0 for an unsupported shape; gpk_i8_mode returns the active mode bits. */
 size_t gpk_i8_workspace_bytes(int NP, int MPmax, int S);

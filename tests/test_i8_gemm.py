@@ -134,6 +134,26 @@ def test_kernel_control_flow_model_matches_the_arithmetic(S, KB):
     assert np.array_equal(kernel_model(Lo, Q, S, a_tri=1, KB=KB), gemm_nt_sliced(Lo, Q, S))
 
 
+def test_tail_scratch_regions_of_the_right_most_path_fit_one_square_region():
+    """gpk_chol.cu gives every right-most-path node its own slice of the second square region (offset = sum of
+    gpk_i8_pair_bytes(n1, n2, n1) over its ancestors); the node's second product (M = n2, N = n1, K = n2) re-uses
+    it.  Restated here: the offsets never run past S * NP^2 (+ the scale vector), so no level silently falls
+    back for lack of scratch, and the second product never needs more than the first."""
+    al = lambda b: (b + 255) & ~255
+    pair = lambda S, M, N, K: al(S * M * K) + al(8 * M) + al(S * N * K) + al(8 * N)
+    for S in (6, 7, 8):
+        for NP in list(range(256, 4097, 128)) + [20096, 50048, 65536 - 128]:
+            square = al(S * NP * NP) + al(8 * NP)
+            off, n = 0, NP
+            while n > 128:
+                n1 = 128 * ((n // 128 + 1) // 2)
+                n2 = n - n1
+                need = pair(S, n1, n2, n1)
+                assert pair(S, n2, n1, n2) <= need
+                assert off + need <= square, (S, NP, n)
+                off, n = off + need, n2
+
+
 # ------------------------------------------------------------------------------------------------ GPU (opt-in)
 _gated = pytest.mark.skipif(os.environ.get("GPK_I8_EXPERIMENT") != "1",
                             reason="experimental tcgen05 int8 path: set GPK_I8_EXPERIMENT=1 (never run on a GPU yet)")
@@ -244,14 +264,17 @@ def _path_case(n=1000, d=9, t=3, seed=5):
 
 @pytest.mark.gpu
 @_gated
+@pytest.mark.parametrize("mode", [3, 7])
 @pytest.mark.parametrize("theta_shift", [0.0, -1.5])
-def test_estimator_path_with_int8_lauum_and_predict(monkeypatch, theta_shift):
-    """GPK_I8=3 routes K^-1 (objective gradient) and predict's variance contraction through the int8 kernel; the
-    FP64 DMMA run of the same estimator is the yardstick (tolerances from tools/ozaki_study.py at 7 slices)."""
+def test_estimator_path_with_int8_contractions(monkeypatch, theta_shift, mode):
+    """GPK_I8 bit 1 routes K^-1 (objective gradient), bit 2 predict's variance contraction, bit 4 the right-most-path
+    inverse products of objective evaluations through the int8 kernel; the FP64 DMMA run of the same estimator is
+    the yardstick (tolerances from tools/ozaki_study.py at 7 slices)."""
     from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
     from unmanned_aerial_vehicles_b200 import GaussianProcessRegressor, _lib
     X, Y, Xq = _path_case()
     k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 9, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0))
+    monkeypatch.setenv("GPK_I8_TAIL_MIN", "128")             # N=1000: every level of the right-most path qualifies
 
     def run():
         g = GaussianProcessRegressor(kernel=k, alpha=1e-6, optimizer=None).fit(X, Y)
@@ -264,10 +287,15 @@ def test_estimator_path_with_int8_lauum_and_predict(monkeypatch, theta_shift):
     monkeypatch.delenv("GPK_I8", raising=False)
     lml0, grad0, m0, s0, m10, s10, g0 = run()
     assert g0._engine.i8_mode == 0 and _lib.load().gpk_i8_mode() == 0
-    monkeypatch.setenv("GPK_I8", "3")
+    monkeypatch.setenv("GPK_I8", str(mode))
     lml1, grad1, m1, s1, m11, s11, g1 = run()
-    assert g1._engine.i8_mode == 3 and _lib.load().gpk_i8_mode() == 3
-    assert lml1 == lml0 and np.array_equal(m1, m0)           # factor, alpha and mean never leave FP64
+    assert g1._engine.i8_mode == mode and _lib.load().gpk_i8_mode() == mode
+    if mode & 4:                                             # alpha of the EVALUATION goes through the emulated tail
+        assert abs(lml1 - lml0) <= 1e-9 * abs(lml0)
+    else:
+        assert lml1 == lml0                                  # factor and alpha never leave FP64
+    assert np.array_equal(m1, m0)                            # the final factorisation is all-FP64 in every mode
+    assert np.array_equal(g1.alpha_, g0.alpha_) and np.array_equal(g1.L_, g0.L_)
     np.testing.assert_allclose(grad1, grad0, rtol=1e-8, atol=1e-8 * np.abs(grad0).max())
     np.testing.assert_allclose(s1, s0, rtol=0, atol=1e-9)
     assert np.array_equal(m11, m10) and np.array_equal(s11, s10)
@@ -276,4 +304,4 @@ def test_estimator_path_with_int8_lauum_and_predict(monkeypatch, theta_shift):
     np.testing.assert_array_equal(g0.predict(Xq, return_std=True)[1], s0)
     assert _lib.load().gpk_i8_mode() == 0
     np.testing.assert_array_equal(g1.predict(Xq, return_std=True)[1], s1)
-    assert _lib.load().gpk_i8_mode() == 3
+    assert _lib.load().gpk_i8_mode() == mode

@@ -21,6 +21,7 @@ cudaError_t gpk_launch_extract_lower(const double*, int, double*, int, cudaStrea
 cudaError_t gpk_launch_pad_copy(const double*, int, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_copy_diag(const double*, int, int, double*, cudaStream_t);
 cudaError_t gpk_launch_potrf_inv(double*, int, double*, double*, int, int, int*, cudaStream_t);
+cudaError_t gpk_launch_potrf_inv_ex(double*, int, double*, double*, int, int, int*, cudaStream_t, bool);
 cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
 cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
@@ -109,7 +110,7 @@ int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double
   double* diag = ws_d + nt * nt * (size_t)(gpk_dp_of(D) + 2);
   gpk_i8_invalidate();
   GPK_CHECK(gpk_launch_gram(X_d, N, D, p, A_d, NP, 1, st));
-  GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st));
+  GPK_CHECK(gpk_launch_potrf_inv_ex(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st, (gpk_i8_mode() & 4) != 0));
   GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, st));
   GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, st));
   GPK_CHECK(gpk_launch_copy_diag(A_d, NP, NP, diag, st));

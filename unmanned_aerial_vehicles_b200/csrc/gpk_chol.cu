@@ -351,9 +351,14 @@ static cudaError_t chol_side_init(CholSide& cs) {
 }
 
 struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err;
-                 CholSide* side; };
+                 CholSide* side; bool i8_tail; };
 
-static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
+static inline cudaError_t i8_rc_to_cuda(int rc) { return rc <= -1000 ? (cudaError_t)(-rc - 1000) : cudaErrorInvalidValue; }
+
+// rm: this node lies on the right-most path of the recursion (root, root.22, root.22.22, ...).  The two inverse
+// products of such a node are read by no later L21 -- only by K^-1 and predict -- so with the opt-in int8 tail
+// (CholCtx::i8_tail) they may run on the tcgen05 pipe; i8_off is this node's scratch offset.
+static void chol_rec(CholCtx& c, int off, int n, int depth = 0, bool rm = true, size_t i8_off = 0) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
     if ((c.err = leaf_configure()) != cudaSuccess) return;
@@ -362,8 +367,9 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
     return;
   }
   const int n1 = GPK_TILE * ((n / GPK_TILE + 1) / 2), n2 = n - n1, o2 = off + n1;
-  chol_rec(c, off, n1, depth + 1);
+  chol_rec(c, off, n1, depth + 1, false, 0);
   if (c.err != cudaSuccess) return;
+  const bool tail = c.i8_tail && rm;
   double* A21 = c.A + (size_t)o2 * c.lda + off;
   double* Ml21 = c.Ml + (size_t)o2 * c.ldm + off;
   double* Mu12 = c.Mu + (size_t)off * c.ldm + o2;
@@ -384,8 +390,16 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   GpkGemmArgs w{};
   w.A = c.Mu + (size_t)off * c.ldm + off; w.lda = c.ldm; w.B = A21; w.ldb = c.lda; w.C = Mu12; w.ldc = c.ldm;
   w.M = n1; w.N = n2; w.K = n1; w.alpha = 1.0; w.a_tri = GPK_TRI_UPPER; w.epilogue = GPK_EPI_STORE;
+  auto launch_w = [&](cudaStream_t s) -> cudaError_t {
+    if (tail) {
+      const int took = gpk_i8_try_gemm(w.A, w.lda, w.a_tri, w.B, w.ldb, w.b_tri, w.M, w.N, w.K, w.alpha, w.C, w.ldc, i8_off, s);
+      if (took < 0) return i8_rc_to_cuda(took);
+      if (took) return cudaSuccess;
+    }
+    return gpk_launch_gemm_nt(w, s);
+  };
   if (fork) {
-    if ((c.err = gpk_launch_gemm_nt(w, ws)) != cudaSuccess) return;
+    if ((c.err = launch_w(ws)) != cudaSuccess) return;
     if ((c.err = cudaEventRecord(c.side->join[depth], ws)) != cudaSuccess) return;
   }
   // A22 -= L21 L21^T (lower tiles)
@@ -393,23 +407,30 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   g.A = A21; g.lda = c.lda; g.B = A21; g.ldb = c.lda; g.C = c.A + (size_t)o2 * c.lda + o2; g.ldc = c.lda;
   g.M = n2; g.N = n2; g.K = n1; g.alpha = -1.0; g.accumulate = 1; g.lower_only = 1; g.epilogue = GPK_EPI_STORE;
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
-  chol_rec(c, o2, n2, depth + 1);
+  chol_rec(c, o2, n2, depth + 1, rm, tail ? i8_off + gpk_i8_pair_bytes(n1, n2, n1) : 0);
   if (c.err != cudaSuccess) return;
   if (fork) {
     if ((c.err = cudaStreamWaitEvent(c.st, c.side->join[depth], 0)) != cudaSuccess) return;
   } else {
-    if ((c.err = gpk_launch_gemm_nt(w, c.st)) != cudaSuccess) return;
+    if ((c.err = launch_w(c.st)) != cudaSuccess) return;
   }
   // M21 = -M22 * W  : C[m,j] = -sum_k M22[m,k] Wt[j,k]
   g = GpkGemmArgs{};
   g.A = c.Ml + (size_t)o2 * c.ldm + o2; g.lda = c.ldm; g.B = Mu12; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
   g.M = n2; g.N = n1; g.K = n2; g.alpha = -1.0; g.a_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_STORE;
-  if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
+  int took = 0;
+  if (tail) {   // the planes of this node's first product are dead by now (joined above): same region
+    took = gpk_i8_try_gemm(g.A, g.lda, g.a_tri, g.B, g.ldb, g.b_tri, g.M, g.N, g.K, g.alpha, g.C, g.ldc, i8_off, c.st);
+    if (took < 0) { c.err = i8_rc_to_cuda(took); return; }
+  }
+  if (!took && (c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
   c.err = gpk_launch_transpose_block(Ml21, c.ldm, Mu12, c.ldm, n2, n1, c.st);
 }
 
-cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
-                                 cudaStream_t st) {
+// i8_tail: objective evaluations only (gpk_lml_eval, opt-in mode bit 4); the final factorisation predict reads
+// (gpk_potrf_inv) always keeps an all-FP64 inverse.
+cudaError_t gpk_launch_potrf_inv_ex(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
+                                    cudaStream_t st, bool i8_tail) {
   if (NP % GPK_TILE) return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
@@ -419,9 +440,14 @@ cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, 
     side = &g_cs[gpk_current_device()];
     if ((e = chol_side_init(*side)) != cudaSuccess) return e;
   }
-  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side};
+  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side, i8_tail};
   chol_rec(c, 0, NP);
   return c.err;
+}
+
+cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
+                                 cudaStream_t st) {
+  return gpk_launch_potrf_inv_ex(A, lda, Mlow, Mup, ldm, NP, info, st, false);
 }
 
 // K^-1 = L^-T L^-1 = Mup * Mup^T  (lower tiles of Kinv are written; diagonal tiles in full)

@@ -57,6 +57,9 @@ struct GpkI8State { char* ws; size_t bytes; int NP, MPmax, S, mode; const double
 extern "C" int gpk_i8_mode();            // 0 unless gpk_i8_configure() enabled something on the current device
 extern "C" void gpk_i8_invalidate();     // the L^-1 whose planes were prepared for predict is about to change
 int gpk_i8_try_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, cudaStream_t st);
+int gpk_i8_try_gemm(const double* A, int lda, int a_tri, const double* B, int ldb, int b_tri, int M, int N, int K,
+                    double alpha, double* C, int ldc, size_t region_off, cudaStream_t st);
+size_t gpk_i8_pair_bytes(int M, int N, int K);   // scratch one gpk_i8_try_gemm takes from its region (0: tail mode off)
 int gpk_i8_try_predict_rowsq(const double* Ks, int MP, const double* Mlow, int NP, double* rowsq, cudaStream_t st);
 
 extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)

@@ -409,7 +409,8 @@ int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const s
 
 // ---------------------------------------------------------------------------------------------- opt-in use on the path
 // Nothing below runs unless gpk_i8_configure() has registered scratch on the current device (engine.py does that
-// only when GPK_I8 is set).  mode bit 1: K^-1 = L^-T L^-1 (LAUUM) of gpk_lml_eval; bit 2: predict's Ks L^-T.
+// only when GPK_I8 is set).  mode bit 1: K^-1 = L^-T L^-1 (LAUUM) of gpk_lml_eval; bit 2: predict's Ks L^-T;
+// bit 4: right-most-path inverse products inside gpk_lml_eval's factorisation.
 static GpkI8State g_i8[GPK_MAX_DEV];
 
 static inline size_t i8_align(size_t b) { return (b + 255) & ~(size_t)255; }
@@ -464,6 +465,44 @@ int gpk_i8_try_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, 
   int rc = gpk_i8_slice(Mup, ldm, NP, NP, GPK_TRI_UPPER, g.S, planes, NP, NP, mu, st);
   if (rc) return rc;
   rc = gpk_i8_gemm_nt(planes, mu, NP, planes, mu, NP, NP, g.S, Kinv, ldk, 1.0, 0, GPK_TRI_UPPER, GPK_TRI_UPPER, 1, nullptr, st);
+  return rc ? rc : 1;
+}
+
+// Right-most-path inverse products of the recursive factorisation (mode bit 4; gpk_chol.cu): C (M x N) = alpha A B^T
+// from FP64 blocks with leading dimensions, planes carved from the second square region at region_off (one
+// region per recursion depth, so the product a side stream still runs never shares planes with a deeper level;
+// LAUUM re-uses the region afterwards, stream-ordered behind all of them).  Same return convention.
+static int i8_tail_min() {
+  static int v = 0;
+  if (!v) { const char* e = getenv("GPK_I8_TAIL_MIN"); v = (e && atoi(e) >= I8_BM) ? atoi(e) : 1024; }
+  return v;
+}
+
+size_t gpk_i8_pair_bytes(int M, int N, int K) {
+  const GpkI8State& g = g_i8[gpk_current_device()];
+  if (!(g.mode & 4)) return 0;
+  return i8_align((size_t)g.S * M * K) + i8_align(sizeof(double) * (size_t)M) + i8_align((size_t)g.S * N * K) +
+         i8_align(sizeof(double) * (size_t)N);
+}
+
+int gpk_i8_try_gemm(const double* A, int lda, int a_tri, const double* B, int ldb, int b_tri, int M, int N, int K,
+                    double alpha, double* C, int ldc, size_t region_off, cudaStream_t st) {
+  GpkI8State& g = g_i8[gpk_current_device()];
+  if (!(g.mode & 4) || M % I8_BM || N % I8_BN || K % I8_KPAD) return 0;
+  if (M < i8_tail_min() || N < i8_tail_min() || K < i8_tail_min()) return 0;
+  const size_t need = gpk_i8_pair_bytes(M, N, K);
+  if (region_off + need > i8_square_bytes(g.NP, g.S)) return 0;
+  char* base = g.ws + i8_square_bytes(g.NP, g.S) + region_off;
+  signed char* pa = (signed char*)base;
+  double* mua = (double*)(base + i8_align((size_t)g.S * M * K));
+  char* bb = (char*)mua + i8_align(sizeof(double) * (size_t)M);
+  signed char* pb = (signed char*)bb;
+  double* mub = (double*)(bb + i8_align((size_t)g.S * N * K));
+  int rc = gpk_i8_slice(A, lda, M, K, a_tri, g.S, pa, M, K, mua, st);
+  if (rc) return rc;
+  rc = gpk_i8_slice(B, ldb, N, K, b_tri, g.S, pb, N, K, mub, st);
+  if (rc) return rc;
+  rc = gpk_i8_gemm_nt(pa, mua, M, pb, mub, N, K, g.S, C, ldc, alpha, 0, a_tri, b_tri, 0, nullptr, st);
   return rc ? rc : 1;
 }
 

@@ -76,7 +76,7 @@ class DeviceGP:
 
     def _configure_i8(self):
         """EXPERIMENTAL, off unless GPK_I8 is set (bit 1: K^-1 of the objective, bit 2: predict's variance
-        contraction; GPK_I8_SLICES, default 7): allocates the scratch libgpk's int8-sliced tcgen05 contraction needs
+        contraction, bit 4: right-most-path inverse products of the objective; GPK_I8_SLICES, default 7): allocates the scratch libgpk's int8-sliced tcgen05 contraction needs
         (DESIGN.md section 8).  A shape it cannot take is an error here, not a silent fall back."""
         self.i8_mode = 0
         self._i8_planes_ok = False
