@@ -292,6 +292,11 @@ def b200_arm(args):
                     "d2h_bytes_per_step": d2h},
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
         }
+        if getattr(eng, "i8_mode", 0):   # opt-in experiment: a line measured through it says so (never the default)
+            line["dtype"] = "f64 with int8-sliced emulation on parts of the path"
+            line["config"]["int8_emulation"] = {"GPK_I8": eng.i8_mode, "slices": int(os.environ.get("GPK_I8_SLICES", "7")),
+                                                "note": "bit 1 LAUUM, bit 2 predict variance, bit 4 right-most-path "
+                                                        "inverse products; roofline block still times the DMMA kernel only"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
