@@ -287,24 +287,25 @@ gpk_i8_slice_kernel(const double* __restrict__ src, int ld, int rows, int K, int
 
   const size_t plane = (size_t)rowsP * KP;
   int8_t* out = planes + (size_t)r * KP;
-  for (int k0 = threadIdx.x * 16; k0 < KP; k0 += 256 * 16) {     // 16 consecutive k per thread: one 16-byte store per plane
-    double rr[16];
+  // 4 consecutive k per thread: a warp reads 1 KB of the row and writes 128 contiguous bytes of every plane
+  for (int k0 = threadIdx.x * 4; k0 < KP; k0 += 256 * 4) {
+    double rr[4];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
+    for (int j = 0; j < 4; ++j) {
       const int k = k0 + j;
       rr[j] = (k >= k_lo && k < k_hi) ? row[k] * inv_mu : 0.0;
     }
     for (int s = 0; s < S; ++s) {
       const double up = (s == 0) ? 64.0 : 128.0;
-      uint32_t w[4] = {0u, 0u, 0u, 0u};
+      uint32_t w = 0u;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
+      for (int j = 0; j < 4; ++j) {
         const double x = rr[j] * up;
         const double qd = rint(x);
         rr[j] = x - qd;
-        w[j >> 2] |= ((uint32_t)(uint8_t)(int8_t)(int)qd) << (8 * (j & 3));
+        w |= ((uint32_t)(uint8_t)(int8_t)(int)qd) << (8 * j);
       }
-      *reinterpret_cast<uint4*>(out + (size_t)s * plane + k0) = make_uint4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<uint32_t*>(out + (size_t)s * plane + k0) = w;
     }
   }
 }
