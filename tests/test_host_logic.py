@@ -84,3 +84,19 @@ def test_with_theta_equals_lowering_the_cloned_kernel(k, d):
     assert np.array_equal(template.length_scale, lower(k, d).length_scale)               # template untouched
     with pytest.raises(ValueError):
         template.with_theta(np.zeros(len(k.theta) + 1))
+
+
+@pytest.mark.parametrize("G", [1, 3, 8, 16, 24])
+@pytest.mark.parametrize("ntm,ntn", [(1, 1), (7, 5), (8, 8), (19, 11), (128, 128)])
+def test_gemm_raster_map_is_a_bijection(G, ntm, ntn):
+    """Model of the tile raster of gpk_gemm_nt_kernel (csrc/gpk_gemm.cu: groups of G tile-rows, column-major inside a
+    group; G = 8 unless GPK_GEMM_RASTER is set): every (tm, tn) is visited exactly once for any group height,
+    including a ragged last group."""
+    seen = set()
+    for ident in range(ntm * ntn):
+        grp, within = divmod(ident, G * ntn)
+        gsz = min(G, ntm - grp * G)
+        tm, tn = grp * G + within % gsz, within // gsz
+        assert 0 <= tm < ntm and 0 <= tn < ntn
+        seen.add((tm, tn))
+    assert len(seen) == ntm * ntn

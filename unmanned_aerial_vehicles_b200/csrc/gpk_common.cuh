@@ -41,6 +41,7 @@ struct GpkGemmArgs {
   int lower_only;             // skip tiles strictly above the diagonal (needs M == N)
   int epilogue;               // GPK_EPI_*
   double* rowsq;              // GPK_EPI_ROWSUMSQ: (M x N/GPK_TILE) partial row sums of squares
+  int raster_rows;            // tile-rows per raster group; 0 = the launcher's default (8, or GPK_GEMM_RASTER)
 };
 
 // internal launchers (C++ linkage), all asynchronous on `st`

@@ -46,13 +46,15 @@ template <int TS, int WR, int WC>
 __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt_kernel(GpkGemmArgs g) {
   constexpr int NTHR = 32 * WR * WC, MT = TS / WR / 8, NT = TS / WC / 8, STAGE_DOUBLES = 2 * TS * LDSM;
   extern __shared__ __align__(16) double smem[];
-  // grouped raster: 8 tile-rows per group, column-major inside a group, so co-resident CTAs share A and B panels in L2
+  // grouped raster: G tile-rows per group (8 unless GPK_GEMM_RASTER says otherwise), column-major inside a group,
+  // so co-resident CTAs share A and B panels in L2
   int tn, tm;
   {
+    const int G = g.raster_rows;
     const int ntn = gridDim.x, ntm = gridDim.y, id = blockIdx.y * ntn + blockIdx.x;
-    const int grp = id / (8 * ntn), within = id - grp * 8 * ntn;
-    const int gsz = min(8, ntm - grp * 8);
-    tm = grp * 8 + within % gsz;
+    const int grp = id / (G * ntn), within = id - grp * G * ntn;
+    const int gsz = min(G, ntm - grp * G);
+    tm = grp * G + within % gsz;
     tn = within / gsz;
   }
   if (g.lower_only && tn > tm) return;
@@ -161,7 +163,13 @@ __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt
 }
 
 template <int TS, int WR, int WC>
-static cudaError_t launch_ts(const GpkGemmArgs& g, cudaStream_t st) {
+static cudaError_t launch_ts(const GpkGemmArgs& g_in, cudaStream_t st) {
+  // tuning hook (tools/gemm_raster_sweep.py): GPK_GEMM_RASTER=G tile-rows per raster group.  The A panel of a group
+  // (G*TS rows x K) is what has to stay in the 126 MB L2 while B streams past it once per group, so a larger G
+  // cuts B's DRAM re-reads (ntm/G passes) until that panel no longer fits.  Default 8: the measured configuration.
+  static const int raster_env = [] { const char* e = getenv("GPK_GEMM_RASTER"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 0; }();
+  GpkGemmArgs g = g_in;
+  if (g.raster_rows <= 0) g.raster_rows = raster_env ? raster_env : 8;
   static bool attr_set[GPK_MAX_DEV] = {false};
   const int dev = gpk_current_device();
   if (!attr_set[dev]) {
