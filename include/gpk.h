@@ -85,6 +85,25 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
                 const double* y_std_d, double* mean_h, double* std_h, int* neg_h, double* ws_d, size_t ws_doubles,
                 void* stream);
 
+/* The same for several models that answer the SAME number of query rows each -- the six per-output members (each
+ * with its own input scaler, hence its own Xq_h) of the reference's schema B / C pickles: pretrained_gp.py:52-98
+ * loops `for name in models: scaler.transform; gp.predict(return_std=True)`, gp_enhanced_mpc.py:150-183 the same.
+ * ONE call, ONE stream sync: every model's H2D + launches are enqueued before the first D2H copy.  Fields as the
+ * gpk_predict arguments of the same names; each model brings its own scratch (ws_d must differ between models);
+ * std_h / neg_h may be NULL per model.  n_models <= GPK_MAX_STACKED. */
+#define GPK_MAX_STACKED 16
+typedef struct GpkStackedModel {
+  const double* Xq_h; int D;
+  const double* X_d; int N;
+  const double* inv_ls_h; double c; double noise;
+  const double* alpha_d; int T;
+  const double* Mlow_d; int NP;
+  const double* y_mean_d; const double* y_std_d;
+  double* mean_h; double* std_h; int* neg_h;
+  double* ws_d; size_t ws_doubles;
+} GpkStackedModel;
+int gpk_predict_stacked(const GpkStackedModel* models_h, int n_models, int Mq, void* stream);
+
 /* utilities */
 int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream);
 int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream);

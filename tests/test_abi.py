@@ -63,3 +63,37 @@ def test_int8_opt_in_registration_is_pure_host_and_off_by_default():
     assert lib.gpk_i8_configure(fake, want, NP, MP, 8, 3) != 0 and lib.gpk_i8_mode() == 0
     assert lib.gpk_i8_configure(fake, want, NP, MP, S, 3) == 0 and lib.gpk_i8_mode() == 3
     assert lib.gpk_i8_configure(None, 0, 0, 0, 0, 0) == 0 and lib.gpk_i8_mode() == 0
+
+
+def test_stacked_predict_argument_block_is_marshalled_field_by_field():
+    """gpk_predict_stacked validates every model's arguments before its first CUDA call, so the ctypes mirror of
+    GpkStackedModel can be checked without a GPU: break one field at a time and read the code that field's check
+    returns (same codes as gpk_predict)."""
+    lib = _lib.load()
+    fake = 0x1000                                                             # never dereferenced: validation only
+    inv = _lib.darr([1.0] * 9)
+
+    def model(**kw):
+        arr = (_lib.StackedModel * 1)()
+        m = arr[0]
+        m.Xq_h, m.D, m.X_d, m.N = fake, 9, fake, 1000
+        m.inv_ls_h, m.c, m.noise = ctypes.cast(inv, ctypes.c_void_p), 1.0, 0.1
+        m.alpha_d, m.T, m.Mlow_d, m.NP = fake, 3, fake, 1024
+        m.y_mean_d, m.y_std_d, m.mean_h, m.std_h, m.neg_h = fake, fake, fake, fake, fake
+        m.ws_d, m.ws_doubles = fake, 0                                         # too little scratch: -19 when all else is fine
+        for k, v in kw.items():
+            setattr(m, k, v)
+        return arr
+
+    call = lambda arr, n=1, mq=25: lib.gpk_predict_stacked(arr, n, mq, None)
+    assert call(None) == -1
+    assert call(model(), n=0) == -2 and call(model(), n=_lib.MAX_STACKED + 1) == -2
+    assert call(model(), mq=0) == -3
+    assert call(model()) == -19                                               # every other field passed its check
+    need = lib.gpk_predict_workspace_doubles(128, 1024, 9, 3)
+    assert call(model(ws_doubles=need - 1)) == -19
+    assert call(model(mean_h=None)) == -1 and call(model(Xq_h=None)) == -1 and call(model(ws_d=None)) == -1
+    assert call(model(NP=1000)) == -12 and call(model(NP=896)) == -12         # not a multiple of 128 / smaller than N
+    assert call(model(T=0)) == -10
+    assert call(model(D=33, ws_doubles=1 << 40)) == -3                        # more than 32 features
+    assert call(model(inv_ls_h=None, ws_doubles=1 << 40)) == -3

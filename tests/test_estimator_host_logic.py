@@ -238,3 +238,81 @@ def test_int8_scratch_ownership_protocol_between_engines_on_one_device():
     only_lauum._i8_bind(need_planes=True)                        # mode without the predict bit never slices L^-1
     assert calls[9:] == [("configure", 0x4000, 1)]
     eng_mod._I8_OWNER.clear()
+
+
+@pytest.mark.parametrize("return_std", [False, True])
+def test_predict_stacked_equals_the_per_model_loop(monkeypatch, return_std):
+    """gpr.predict_stacked (one device call for the per-output members of schema B / C pickles): same values and
+    shapes as calling predict on each member, through the stacked engine hook when the engines offer one and through
+    the loop when they do not or when a member does not qualify."""
+    X, Y = _data(120, 4, 3, seed=3)
+    k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 4, (0.1, 10)) + WhiteKernel(0.05, (1e-5, 10))
+    models = []
+    for t in range(3):
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            models.append(gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, optimizer=None,
+                                                           normalize_y=bool(t % 2)).fit(X * (1 + t), Y[:, t]))
+    Xs = [np.ascontiguousarray(X[:17] * (1 + t) + 0.01) for t in range(3)]
+    want = [m.predict(x, return_std=return_std) for m, x in zip(models, Xs)]
+
+    def same(got):
+        for g, w in zip(got, want):
+            if return_std:
+                assert g[0].shape == w[0].shape and g[1].shape == w[1].shape
+                np.testing.assert_array_equal(g[0], w[0]); np.testing.assert_array_equal(g[1], w[1])
+            else:
+                assert g.shape == w.shape
+                np.testing.assert_array_equal(g, w)
+
+    same(gpr_mod.predict_stacked(models, Xs, return_std=return_std))          # OracleEngine has no hook: the loop
+    calls = []
+
+    def hook(engines, Xqs, scales, rs):
+        calls.append(len(engines))
+        return [e.predict(x, s[0], s[1], rs)[:2] + (0,) for e, x, s in zip(engines, Xqs, scales)]
+
+    monkeypatch.setattr(OracleEngine, "predict_stacked", staticmethod(hook), raising=False)
+    same(gpr_mod.predict_stacked(models, Xs, return_std=return_std))
+    assert calls == [3]
+    same(gpr_mod.predict_stacked(models, [x.tolist() for x in Xs], return_std=return_std))   # lists: validated loop
+    assert calls == [3]
+    monkeypatch.setattr(OracleEngine, "predict_stacked", staticmethod(lambda *a: None), raising=False)
+    same(gpr_mod.predict_stacked(models, Xs, return_std=return_std))          # hook declines: the loop
+
+
+def test_per_output_members_with_scalers_match_the_reference_loop():
+    """PerOutputGP.predict_batch (pretrained_gp.py:52-98 / gp_enhanced_mpc.py:150-183): sklearn-fitted members and
+    StandardScalers from a schema-B pickle; the scaler shortcut must be bit-identical to scaler.transform /
+    inverse_transform, the values equal to the reference's per-output loop run with stock sklearn."""
+    from sklearn.preprocessing import MinMaxScaler, StandardScaler
+
+    from unmanned_aerial_vehicles_b200 import callers
+
+    X, Y = _data(150, 5, 3, seed=11)
+    X = X * np.array([1.0, 5.0, 0.2, 3.0, 1.0]) + np.array([0.0, 2.0, -1.0, 0.5, 10.0])
+    names = ["vx_residual", "vy_residual", "vz_residual"]
+    models, sX, sY = {}, {}, {}
+    for i, n in enumerate(names):
+        sX[n] = (StandardScaler() if i < 2 else MinMaxScaler()).fit(X)       # third member: not the shortcut
+        sY[n] = StandardScaler().fit(Y[:, i:i + 1])
+        k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 5, (0.1, 10)) + WhiteKernel(0.01, (1e-5, 10))
+        models[n] = SkGPR(kernel=k, alpha=1e-6, optimizer=None).fit(sX[n].transform(X), sY[n].transform(Y[:, i:i + 1]).ravel())
+    pg = callers.adopt_pickle(pickle.loads(pickle.dumps({"gp_models": models, "scalers_X": sX, "scalers_y": sY})))
+    pg.names = ["x_residual"] + names
+    Xq = X[:25] + 0.01
+    for n in names[:2]:
+        np.testing.assert_array_equal(pg._scale_in(sX[n], Xq), sX[n].transform(Xq))
+        m = np.linspace(-1, 1, 25)
+        np.testing.assert_array_equal(pg._scale_out(sY[n], m), sY[n].inverse_transform(m.reshape(-1, 1)).ravel())
+    mean, std = pg.predict_batch(Xq)
+    assert not mean[:, 0].any() and (std[:, 0] == 1e6).all()
+    for i, n in enumerate(names, start=1):
+        ms, ss = models[n].predict(sX[n].transform(Xq), return_std=True)
+        np.testing.assert_allclose(mean[:, i], sY[n].inverse_transform(ms.reshape(-1, 1)).ravel(), rtol=1e-6, atol=1e-9)
+        np.testing.assert_allclose(std[:, i], np.abs(ss * sY[n].scale_[0]), rtol=0, atol=1e-8)
+    mean2, none = pg.predict_batch(Xq, return_std=False)
+    assert none is None
+    np.testing.assert_allclose(mean2, mean, rtol=1e-12, atol=1e-14)
+    with pytest.raises(ValueError):
+        pg.predict_batch(np.full((2, 5), np.nan))

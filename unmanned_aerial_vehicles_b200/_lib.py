@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("GPK_LIB", os.path.join(_HERE, "libgpk.so"))
 SYMBOLS = (
     "gpk_abi_version", "gpk_pad", "gpk_lml_out_len", "gpk_grad_workspace_doubles", "gpk_gram",
     "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
-    "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
+    "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict", "gpk_predict_stacked", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
     "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_leaf_phase_cycles", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
     "gpk_i8_slice", "gpk_i8_gemm_nt", "gpk_i8_workspace_bytes", "gpk_i8_configure", "gpk_i8_prepare_predict", "gpk_i8_mode",
 )
@@ -36,6 +36,16 @@ _d = C.c_double
 _dp = C.POINTER(C.c_double)
 
 
+MAX_STACKED = 16   # GPK_MAX_STACKED in include/gpk.h
+
+
+class StackedModel(C.Structure):
+    """GpkStackedModel of include/gpk.h: one model's arguments of gpk_predict_stacked"""
+    _fields_ = [("Xq_h", _p), ("D", _i), ("X_d", _p), ("N", _i), ("inv_ls_h", _p), ("c", _d), ("noise", _d),
+                ("alpha_d", _p), ("T", _i), ("Mlow_d", _p), ("NP", _i), ("y_mean_d", _p), ("y_std_d", _p),
+                ("mean_h", _p), ("std_h", _p), ("neg_h", _p), ("ws_d", _p), ("ws_doubles", C.c_size_t)]
+
+
 def _declare(lib):
     lib.gpk_abi_version.restype = _i
     lib.gpk_pad.argtypes = [_i]
@@ -54,6 +64,7 @@ def _declare(lib):
     lib.gpk_predict_workspace_doubles.argtypes = [_i, _i, _i, _i]
     lib.gpk_predict_workspace_doubles.restype = C.c_size_t
     lib.gpk_predict.argtypes = [_p, _i, _i, _p, _i, _dp, _d, _d, _p, _i, _p, _i, _p, _p, _p, _p, _p, _p, C.c_size_t, _p]
+    lib.gpk_predict_stacked.argtypes = [C.POINTER(StackedModel), _i, _i, _p]
     lib.gpk_extract_lower.argtypes = [_p, _i, _p, _i, _p]
     lib.gpk_pad_copy.argtypes = [_p, _i, _i, _p, _i, _i, _p]
     lib.gpk_gemm_nt.argtypes = [_p, _i, _p, _i, _p, _i, _i, _i, _i, _d, _i, _i, _i, _i, _p]

@@ -18,7 +18,7 @@ from collections import deque
 import numpy as np
 from sklearn.gaussian_process.kernels import RBF, WhiteKernel
 
-from .gpr import GaussianProcessRegressor
+from .gpr import GaussianProcessRegressor, predict_stacked
 
 FEATURE_COLS = ["x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az", "yaw_rate"]
 RESIDUAL_COLS = ["res_dx", "res_dy", "res_dz", "res_dvx", "res_dvy", "res_dvz"]
@@ -191,23 +191,52 @@ class PerOutputGP:
         self.scalers_X, self.scalers_y = scalers_X, scalers_y
         self.is_loaded = True
 
+    @staticmethod
+    def _plain_standard_scaler(sc):
+        from sklearn.preprocessing import StandardScaler
+        return type(sc) is StandardScaler and sc.with_mean and sc.with_std and getattr(sc, "mean_", None) is not None \
+            and getattr(sc, "scale_", None) is not None
+
+    @classmethod
+    def _scale_in(cls, sc, X):
+        """sc.transform(X); a plain fitted StandardScaler on a float64 matrix is done as its own two array operations
+        ((X - mean_) / scale_, bit-identical) without sklearn's ~180 us of validation per call -- six scalers per
+        control tick in pretrained_gp.py:75 / gp_enhanced_mpc.py:160."""
+        if cls._plain_standard_scaler(sc) and X.shape[1] == sc.mean_.shape[0]:
+            return (X - sc.mean_) / sc.scale_
+        return sc.transform(X)
+
+    @classmethod
+    def _scale_out(cls, sc, m):
+        """sc.inverse_transform(m.reshape(-1, 1)).ravel() (pretrained_gp.py:83-85), same shortcut"""
+        m = np.asarray(m, dtype=np.float64).reshape(-1)
+        if cls._plain_standard_scaler(sc) and sc.mean_.shape[0] == 1:
+            return m * sc.scale_[0] + sc.mean_[0]
+        return sc.inverse_transform(m.reshape(-1, 1)).ravel()
+
     def predict_batch(self, X, return_std=True):
-        """(M, D) -> mean (M, n_outputs), std (M, n_outputs); missing outputs give (0, 1e6) like the reference."""
-        X = np.asarray(X, dtype=np.float64)
+        """(M, D) -> mean (M, n_outputs), std (M, n_outputs); missing outputs give (0, 1e6) like the reference.
+        All members answer in ONE device call (gpr.predict_stacked), each through its own input scaler."""
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        if X.ndim != 2 or not np.isfinite(X).all():
+            from sklearn.utils.validation import check_array
+            X = check_array(X, ensure_2d=True, dtype=np.float64)          # sklearn's own errors for bad input
         M = len(X)
         mean = np.zeros((M, len(self.names)))
         std = np.full((M, len(self.names)), 1e6)
-        for i, name in enumerate(self.names):
-            if name not in self.models:
-                continue
-            Xs = self.scalers_X[name].transform(X)
+        present = [(i, name) for i, name in enumerate(self.names) if name in self.models]
+        if not present or M == 0:
+            return mean, (std if return_std else None)
+        Xs = [self._scale_in(self.scalers_X[name], X) for _, name in present]
+        outs = predict_stacked([self.models[name] for _, name in present], Xs, return_std=return_std)
+        for (i, name), out in zip(present, outs):
             sy = self.scalers_y[name]
             if return_std:
-                m, s = self.models[name].predict(Xs, return_std=True)
-                std[:, i] = np.abs(s * sy.scale_[0])                      # pretrained_gp.py:87
+                m, s = out
+                std[:, i] = np.abs(np.asarray(s).reshape(-1) * sy.scale_[0])                      # pretrained_gp.py:87
             else:
-                m = self.models[name].predict(Xs)
-            mean[:, i] = sy.inverse_transform(np.asarray(m).reshape(-1, 1)).ravel()
+                m = out
+            mean[:, i] = self._scale_out(sy, m)
         return mean, (std if return_std else None)
 
     def predict_residual(self, state, control):

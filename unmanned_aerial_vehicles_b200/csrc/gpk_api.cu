@@ -38,7 +38,7 @@ int gpk_profile_launch_info(int, double*, double*, int*);
 cudaError_t gpk_leaf_cycles(long long* out_h);
 
 static int make_params(GpkKernelParams& p, int D, const double* inv_ls_h, double c, double noise, double jitter) {
-  if (D < 1 || D > GPK_MAXD) return -1;
+  if (D < 1 || D > GPK_MAXD || !inv_ls_h) return -1;
   memset(&p, 0, sizeof(p));
   for (int d = 0; d < D; ++d) p.inv_ls[d] = inv_ls_h[d];
   p.c = c; p.noise = noise; p.jitter = jitter; p.D = D;
@@ -166,11 +166,12 @@ size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T) {
   return (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_ROWSQ_TILE) + 2;
 }
 
-int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
-                double noise, const double* alpha_d, int T, const double* Mlow_d, int NP, const double* y_mean_d,
-                const double* y_std_d, double* mean_h, double* std_h, int* neg_h, double* ws_d, size_t ws_doubles,
-                void* stream) {
-  if (!Xq_h || !mean_h || !ws_d) return -1;
+// one model's share of a host-to-host predict: everything up to (not including) the device->host copies
+static int predict_enqueue(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
+                           double noise, const double* alpha_d, int T, const double* Mlow_d, int NP,
+                           const double* y_mean_d, const double* y_std_d, int want_std, double* ws_d, size_t ws_doubles,
+                           cudaStream_t st, double** mean_d_out, double** std_d_out, int** neg_d_out) {
+  if (!Xq_h || !ws_d) return -1;
   if (Mq < 1) return -2;
   if (NP % GPK_TILE || NP < N) return -12;
   if (T < 1) return -10;
@@ -178,7 +179,6 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
   if (ws_doubles < gpk_predict_workspace_doubles(MP, NP, D, T)) return -19;
   GpkKernelParams p;
   if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -3;
-  cudaStream_t st = (cudaStream_t)stream;
   double* Ks = ws_d;
   double* xq = Ks + (size_t)MP * NP;
   double* mean_d = xq + (size_t)MP * D;
@@ -188,8 +188,7 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
   GPK_CHECK(cudaMemcpyAsync(xq, Xq_h, sizeof(double) * (size_t)Mq * D, cudaMemcpyHostToDevice, st));
   GPK_CHECK(gpk_launch_cross_gram(xq, Mq, X_d, N, D, p, Ks, MP, NP, st));
   GPK_CHECK(gpk_launch_predict_mean(Ks, Mq, N, NP, alpha_d, T, y_mean_d, y_std_d, mean_d, st));
-  GPK_CHECK(cudaMemcpyAsync(mean_h, mean_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
-  if (std_h) {
+  if (want_std) {
     GPK_CHECK(cudaMemsetAsync(neg_d, 0, sizeof(int), st));
     if (gpk_small_batch(Mq, NP)) {
       GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks, Mq, rowsq, st));
@@ -205,8 +204,59 @@ int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, con
       }
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_ROWSQ_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     }
+  }
+  *mean_d_out = mean_d; *std_d_out = std_d; *neg_d_out = neg_d;
+  return 0;
+}
+
+static int predict_readback(int Mq, int T, const double* mean_d, const double* std_d, const int* neg_d, double* mean_h,
+                            double* std_h, int* neg_h, cudaStream_t st) {
+  GPK_CHECK(cudaMemcpyAsync(mean_h, mean_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
+  if (std_h) {
     GPK_CHECK(cudaMemcpyAsync(std_h, std_d, sizeof(double) * (size_t)Mq * T, cudaMemcpyDeviceToHost, st));
     if (neg_h) GPK_CHECK(cudaMemcpyAsync(neg_h, neg_d, sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
+  return 0;
+}
+
+int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
+                double noise, const double* alpha_d, int T, const double* Mlow_d, int NP, const double* y_mean_d,
+                const double* y_std_d, double* mean_h, double* std_h, int* neg_h, double* ws_d, size_t ws_doubles,
+                void* stream) {
+  if (!mean_h) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  double *mean_d, *std_d; int* neg_d;
+  int rc = predict_enqueue(Xq_h, Mq, D, X_d, N, inv_ls_h, c, noise, alpha_d, T, Mlow_d, NP, y_mean_d, y_std_d,
+                           std_h != nullptr, ws_d, ws_doubles, st, &mean_d, &std_d, &neg_d);
+  if (rc) return rc;
+  rc = predict_readback(Mq, T, mean_d, std_d, neg_d, mean_h, std_h, neg_h, st);
+  if (rc) return rc;
+  GPK_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// Several models, the same number of query rows each, ONE call and ONE stream sync: the per-output members of the
+// reference's schema B / C pickles (pretrained_gp.py:52-98, gp_enhanced_mpc.py:150-183).  Every model's launches are
+// enqueued before the first device->host copy, so the host never waits between models.
+int gpk_predict_stacked(const GpkStackedModel* models_h, int n_models, int Mq, void* stream) {
+  if (!models_h) return -1;
+  if (n_models < 1 || n_models > GPK_MAX_STACKED) return -2;
+  if (Mq < 1) return -3;
+  cudaStream_t st = (cudaStream_t)stream;
+  double* mean_d[GPK_MAX_STACKED]; double* std_d[GPK_MAX_STACKED]; int* neg_d[GPK_MAX_STACKED];
+  for (int m = 0; m < n_models; ++m) {
+    const GpkStackedModel& k = models_h[m];
+    if (!k.mean_h) return -1;
+    for (int o = 0; o < m; ++o) if (models_h[o].ws_d == k.ws_d) return -19;   // each model needs its own scratch
+    const int rc = predict_enqueue(k.Xq_h, Mq, k.D, k.X_d, k.N, k.inv_ls_h, k.c, k.noise, k.alpha_d, k.T, k.Mlow_d, k.NP,
+                                   k.y_mean_d, k.y_std_d, k.std_h != nullptr, k.ws_d, k.ws_doubles, st, &mean_d[m],
+                                   &std_d[m], &neg_d[m]);
+    if (rc) { if (m > 0) cudaStreamSynchronize(st); return rc; }   // earlier models' launches still use their buffers
+  }
+  for (int m = 0; m < n_models; ++m) {
+    const GpkStackedModel& k = models_h[m];
+    const int rc = predict_readback(Mq, k.T, mean_d[m], std_d[m], neg_d[m], k.mean_h, k.std_h, k.neg_h, st);
+    if (rc) return rc;
   }
   GPK_CHECK(cudaStreamSynchronize(st));
   return 0;

@@ -272,3 +272,64 @@ class DeviceGP:
             cov[np.diag_indices_from(cov)] += noise
             mean[...] = mean_d[:m].cpu().numpy()
         return mean, std, cov, neg_total
+
+
+def predict_stacked(engines, Xqs, scales, return_std: bool):
+    """Several factored engines on ONE device answer the same number of query rows each in ONE C-ABI call
+    (gpk_predict_stacked: one stream sync for all of them) -- the per-output members of the reference's schema B / C
+    pickles, each seeing the query through its own input scaler (pretrained_gp.py:52-98, gp_enhanced_mpc.py:150-183).
+
+    engines: DeviceGP list; Xqs: one (M, D_k) float64 array per engine; scales: (y_mean, y_std) per engine.
+    Returns [(mean (M,T_k), std (M,T_k) | None, clamped-row count)] in order, or None when the batch does not qualify
+    (different devices, more rows than one chunk, more than MAX_STACKED models, int8 experiment on) -- the caller then
+    loops over DeviceGP.predict, the same kernels one model at a time."""
+    K = len(engines)
+    if K < 1 or K > _lib.MAX_STACKED or len({id(e) for e in engines}) != K:
+        return None
+    dev = engines[0].device
+    M = int(Xqs[0].shape[0])
+    if M < 1 or any(e.device != dev or e.factored is None or getattr(e, "i8_mode", 0) for e in engines):
+        return None
+    if any(x.shape[0] != M for x in Xqs) or any(M > e._chunk_rows_default() for e in engines):
+        return None
+    t = engines[0].torch
+    MP = ((M + 127) // 128) * 128
+    arr = (_lib.StackedModel * K)()
+    keep, out = [], []
+    locks = sorted(engines, key=id)          # one global order, so two stacked callers cannot deadlock
+    for e in locks:
+        e._plock.acquire()
+    try:
+        with t.cuda.device(dev):
+            st = engines[0]._stream()
+            for k, (e, Xq, (y_mean, y_std)) in enumerate(zip(engines, Xqs, scales)):
+                e._i8_bind()
+                Xq = np.ascontiguousarray(Xq, dtype=np.float64)
+                if Xq.shape[1] != e.D:
+                    raise ValueError(f"model {k}: query has {Xq.shape[1]} features, the training set {e.D}")
+                inv_ls, c, noise = e.factored
+                ym, ys = e._target_scale(y_mean, y_std)
+                _, ws_d, ws_n, neg_h = e._predict_ws(MP)
+                inv_h = _lib.darr(inv_ls)
+                mean = np.empty((M, e.T))
+                std = np.empty((M, e.T)) if return_std else None
+                neg_h[0] = 0
+                keep.append((Xq, inv_h, ym, ys, ws_d))
+                out.append((mean, std, neg_h))
+                m = arr[k]
+                m.Xq_h, m.D, m.X_d, m.N = Xq.ctypes.data, e.D, e.X_d.data_ptr(), e.N
+                m.inv_ls_h, m.c, m.noise = C.cast(inv_h, C.c_void_p), c, noise
+                m.alpha_d, m.T, m.Mlow_d, m.NP = e.alpha_d.data_ptr(), e.T, e.Mlow_d.data_ptr(), e.NP
+                m.y_mean_d, m.y_std_d = ym.data_ptr(), ys.data_ptr()
+                m.mean_h = mean.ctypes.data
+                m.std_h = std.ctypes.data if return_std else None
+                m.neg_h = neg_h.ctypes.data if return_std else None
+                m.ws_d, m.ws_doubles = ws_d.data_ptr(), ws_n
+            _lib.check(engines[0].lib.gpk_predict_stacked(arr, K, M, st), "gpk_predict_stacked")
+    finally:
+        for e in locks:
+            e._plock.release()
+    return [(mean, std, int(neg_h[0]) if return_std else 0) for mean, std, neg_h in out]
+
+
+DeviceGP.predict_stacked = staticmethod(predict_stacked)   # gpr.predict_stacked finds it on the engines' class

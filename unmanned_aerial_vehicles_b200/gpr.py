@@ -187,19 +187,21 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         T = eng.T
         scale = self._yscale_b                      # per-target mean/std, broadcast once in _finalize_factor
         mean, std, cov, nneg = eng.predict(X, scale[0], scale[1], return_std, return_cov)
-        y_mean = mean
-        if self.y_train_.ndim == 1 or T == 1:
-            y_mean = mean[:, 0]
         if return_cov:
+            y_mean = mean[:, 0] if (self.y_train_.ndim == 1 or T == 1) else mean
             y_cov = np.outer(cov, np.broadcast_to(self._y_train_std, (T,)) ** 2).reshape(*cov.shape, -1)
             if y_cov.shape[2] == 1:
                 y_cov = np.squeeze(y_cov, axis=2)
             return y_mean, y_cov
+        return self._shape_outputs(mean, std, nneg, return_std)
+
+    def _shape_outputs(self, mean, std, nneg, return_std):
+        """sklearn's output shapes (_gpr.py:453-454, :497-498) and the clamped-variance warning (:485-491)"""
+        y_mean = mean[:, 0] if (self.y_train_.ndim == 1 or mean.shape[1] == 1) else mean
         if return_std:
             if nneg:
                 warnings.warn("Predicted variances smaller than 0. Setting those variances to 0.")
-            y_std = std[:, 0] if std.shape[1] == 1 else std
-            return y_mean, y_std
+            return y_mean, (std[:, 0] if std.shape[1] == 1 else std)
         return y_mean
 
     def sample_y(self, X, n_samples=1, random_state=0):
@@ -280,3 +282,29 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         est._engine = None
         est._low = None
         return est
+
+
+def predict_stacked(models, Xs, return_std=False):
+    """``[m.predict(X, return_std=return_std) for m, X in zip(models, Xs)]`` with ONE device call and ONE stream sync
+    for all of them (``gpk_predict_stacked``) -- the reference's per-output model loops (pretrained_gp.py:66-95,
+    gp_enhanced_mpc.py:150-183, gp_trainer.py:176-179) call ``predict`` once per residual component, each through its
+    own input scaler.  Same kernels as ``predict``, so the results are bit-identical to the loop; batches that do not
+    qualify (an unfitted member, inputs that need sklearn's validation, several devices, more rows than one chunk)
+    take the loop."""
+    models, Xs = list(models), list(Xs)
+    ok = len(models) == len(Xs) and len(models) > 1
+    for m, X in zip(models, Xs):
+        ok = ok and isinstance(m, GaussianProcessRegressor) and hasattr(m, "X_train_") \
+            and type(X) is np.ndarray and X.dtype == np.float64 and X.ndim == 2 and X.size > 0 \
+            and X.shape[1] == m.X_train_.shape[1] and bool(np.isfinite(X).all())
+    if ok:
+        for m in models:
+            m._ensure_factored()
+        engines = [m._engine for m in models]
+        stacked = getattr(type(engines[0]), "predict_stacked", None)
+        res = None
+        if stacked is not None and all(type(e) is type(engines[0]) for e in engines):
+            res = stacked(engines, Xs, [m._yscale_b for m in models], return_std)
+        if res is not None:
+            return [m._shape_outputs(mean, std, nneg, return_std) for m, (mean, std, nneg) in zip(models, res)]
+    return [m.predict(X, return_std=return_std) for m, X in zip(models, Xs)]
