@@ -97,3 +97,63 @@ def test_stacked_predict_argument_block_is_marshalled_field_by_field():
     assert call(model(T=0)) == -10
     assert call(model(D=33, ws_doubles=1 << 40)) == -3                        # more than 32 features
     assert call(model(inv_ls_h=None, ws_doubles=1 << 40)) == -3
+
+
+def test_null_and_shape_arguments_are_refused_before_any_launch():
+    """include/gpk.h: a bad argument returns -k (k = its 1-based position) instead of launching a kernel on it -- a
+    NULL device pointer would otherwise fault the CUDA context for the whole process, and the reference's callers
+    only survive ordinary exceptions (simple_gp.py:199-201)."""
+    lib = _lib.load()
+    f, inv = 0x1000, _lib.darr([1.0] * 9)                                     # f: never dereferenced
+    N, NP, D, T = 1000, 1024, 9, 3
+    assert lib.gpk_gram(None, N, D, inv, 1.0, 0.1, 0.0, f, NP, 1, None) == -1
+    assert lib.gpk_gram(f, N, D, None, 1.0, 0.1, 0.0, f, NP, 1, None) == -3
+    assert lib.gpk_gram(f, N, D, inv, 1.0, 0.1, 0.0, None, NP, 1, None) == -8
+    assert lib.gpk_gram(f, N, D, inv, 1.0, 0.1, 0.0, f, NP + 128, 1, None) == -9
+    assert lib.gpk_potrs(f, f, NP, None, f, f, T, None) == -4
+    assert lib.gpk_potrs(f, f, NP, f, None, f, T, None) == -5
+    assert lib.gpk_potrs(f, f, NP, f, f, None, T, None) == -6
+    ev = [f, N, D, inv, 1.0, 0.1, 1e-6, f, T, f, f, f, f, f, NP, 1, f, f, f, None]
+    for pos in (1, 8, 10, 11, 12, 13, 14, 17, 18, 19):
+        a = list(ev); a[pos - 1] = None
+        assert lib.gpk_lml_eval(*a) == -pos, pos
+    a = list(ev); a[1] = 0
+    assert lib.gpk_lml_eval(*a) == -2
+    a = list(ev); a[8] = 0
+    assert lib.gpk_lml_eval(*a) == -9
+    a = list(ev); a[14] = NP + 128
+    assert lib.gpk_lml_eval(*a) == -15
+    gr = [f, N, D, inv, 1.0, 0.1, f, f, f, T, f, NP, 1, f, f, None]
+    for pos in (1, 7, 8, 9, 11, 14, 15):
+        a = list(gr); a[pos - 1] = None
+        assert lib.gpk_lml_grad(*a) == -pos, pos
+    cg = [f, 25, f, N, D, inv, 1.0, f, 128, NP, None]
+    for pos in (1, 3, 8):
+        a = list(cg); a[pos - 1] = None
+        assert lib.gpk_cross_gram(*a) == -pos, pos
+    pm = [f, 25, N, NP, f, T, f, f, f, None]
+    for pos in (1, 5, 7, 8, 9):
+        a = list(pm); a[pos - 1] = None
+        assert lib.gpk_predict_mean(*a) == -pos, pos
+    ps = [f, 25, 128, f, NP, 1.1, f, T, f, f, f, None]
+    for pos in (1, 4, 7, 9, 10, 11):
+        a = list(ps); a[pos - 1] = None
+        assert lib.gpk_predict_std(*a) == -pos, pos
+    gm = [f, 256, f, 256, f, 256, 256, 256, 256, 1.0, 0, 0, 0, 0, None]
+    for pos in (1, 3, 5):
+        a = list(gm); a[pos - 1] = None
+        assert lib.gpk_gemm_nt(*a) == -pos, pos
+    for pos in (2, 4, 6):
+        a = list(gm); a[pos - 1] = 128                                         # leading dimension shorter than the row
+        assert lib.gpk_gemm_nt(*a) == -pos, pos
+    a = list(gm); a[6] = 200
+    assert lib.gpk_gemm_nt(*a) == -7
+    assert lib.gpk_gemv(f, 128, 128, 128, None, T, f, 1.0, 0.0, 0, None) == -5
+    assert lib.gpk_gemv(f, 128, 128, 128, f, T, None, 1.0, 0.0, 0, None) == -7
+    assert lib.gpk_trimv(f, NP, None, f, T, 0, None) == -3 and lib.gpk_trimv(f, NP, f, None, T, 0, None) == -4
+    assert lib.gpk_fix_diag(None, NP, NP, N, 0.1, 1.0, None) == -1
+    assert lib.gpk_logdiag(None, NP, NP, f, None) == -1 and lib.gpk_logdiag(f, NP, NP, None, None) == -4
+    assert lib.gpk_extract_lower(None, NP, f, N, None) == -1 and lib.gpk_extract_lower(f, NP, None, N, None) == -3
+    assert lib.gpk_extract_lower(f, NP, f, NP + 1, None) == -4
+    assert lib.gpk_pad_copy(None, 10, 10, f, 128, 128, None) == -1 and lib.gpk_pad_copy(f, 10, 10, None, 128, 128, None) == -4
+    assert lib.gpk_dmma_probe(296, 10, None, None, None) == -3

@@ -75,6 +75,7 @@ int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_
 int gpk_potrs(const double* Mlow_d, const double* Mup_d, int NP, const double* y_d, double* u_d, double* alpha_d,
               int T, void* stream) {
   if (!Mlow_d) return -1; if (!Mup_d) return -2; if (NP % GPK_TILE) return -3; if (T < 1) return -7;
+  if (!y_d) return -4; if (!u_d) return -5; if (!alpha_d) return -6;
   GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, (cudaStream_t)stream));
   GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, (cudaStream_t)stream));
   return 0;
@@ -90,9 +91,12 @@ int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double
                  const double* L_d, const double* y_d, const double* alpha_d, int T, const double* Kinv_d, int NP,
                  int with_grad, double* ws_d, double* out_d, void* stream) {
   GpkKernelParams p;
+  if (!X_d) return -1; if (N < 1) return -2;
   if (make_params(p, D, inv_ls_h, c, noise, 0.0)) return -3;
+  if (!L_d) return -7; if (!y_d) return -8; if (!alpha_d) return -9;
   if (T < 1) return -10;
   if (with_grad && !Kinv_d) return -11;
+  if (!ws_d) return -14; if (!out_d) return -15;
   GPK_CHECK(gpk_launch_lml_grad(X_d, N, D, p, L_d, (size_t)NP + 1, y_d, alpha_d, T, Kinv_d, NP, with_grad, ws_d, out_d,
                                 (cudaStream_t)stream));
   return 0;
@@ -103,9 +107,13 @@ int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double
                  int NP, int with_grad, double* ws_d, double* out_d, int* info_d, void* stream) {
   GpkKernelParams p;
   cudaStream_t st = (cudaStream_t)stream;
+  if (!X_d) return -1; if (N < 1) return -2;
   if (make_params(p, D, inv_ls_h, c, noise, jitter)) return -3;
+  if (!y_d) return -8;
   if (T < 1) return -9;
+  if (!A_d) return -10; if (!Mlow_d) return -11; if (!Mup_d) return -12; if (!u_d) return -13; if (!alpha_d) return -14;
   if (NP != gpk_pad(N)) return -15;
+  if (!ws_d) return -17; if (!out_d) return -18; if (!info_d) return -19;
   const size_t nt = (size_t)NP / 64;
   double* diag = ws_d + nt * nt * (size_t)(gpk_dp_of(D) + 2);
   gpk_i8_invalidate();
@@ -128,7 +136,9 @@ int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double
 int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, const double* inv_ls_h, double c,
                    double* Ks_d, int MP, int NP, void* stream) {
   GpkKernelParams p;
-  if (Mq < 1) return -2; if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -5;
+  if (!Xq_d) return -1; if (Mq < 1) return -2; if (!X_d) return -3; if (N < 1) return -4;
+  if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -5;
+  if (!Ks_d) return -8;
   if (MP % 64 || MP < Mq) return -9; if (NP < N || NP % 64) return -10;
   GPK_CHECK(gpk_launch_cross_gram(Xq_d, Mq, X_d, N, D, p, Ks_d, MP, NP, (cudaStream_t)stream));
   return 0;
@@ -136,14 +146,17 @@ int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, 
 
 int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* alpha_d, int T, const double* y_mean_d,
                      const double* y_std_d, double* mean_d, void* stream) {
-  if (!Ks_d) return -1; if (T < 1) return -6;
+  if (!Ks_d) return -1; if (Mq < 1) return -2; if (!alpha_d) return -5; if (T < 1) return -6;
+  if (!y_mean_d) return -7; if (!y_std_d) return -8; if (!mean_d) return -9;
   GPK_CHECK(gpk_launch_predict_mean(Ks_d, Mq, N, NP, alpha_d, T, y_mean_d, y_std_d, mean_d, (cudaStream_t)stream));
   return 0;
 }
 
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
                     const double* y_std_d, int T, double* rowsq_d, double* std_d, int* neg_d, void* stream) {
-  if (MP % GPK_TILE || MP < Mq) return -3; if (NP % GPK_TILE) return -5;
+  if (!Ks_d) return -1; if (Mq < 1) return -2;
+  if (MP % GPK_TILE || MP < Mq) return -3; if (!Mlow_d) return -4; if (NP % GPK_TILE) return -5;
+  if (!y_std_d) return -7; if (T < 1) return -8; if (!rowsq_d) return -9; if (!std_d) return -10; if (!neg_d) return -11;
   if (gpk_small_batch(Mq, NP)) {
     GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks_d, Mq, rowsq_d, (cudaStream_t)stream));
     GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / 32, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
@@ -263,17 +276,21 @@ int gpk_predict_stacked(const GpkStackedModel* models_h, int n_models, int Mq, v
 }
 
 int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream) {
+  if (!src_d) return -1; if (!dst_d) return -3; if (N < 1 || N > NP) return -4;
   GPK_CHECK(gpk_launch_extract_lower(src_d, NP, dst_d, N, (cudaStream_t)stream));
   return 0;
 }
 int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream) {
+  if (!src_d) return -1; if (!dst_d) return -4;
   if (RP < R) return -5; if (CP < C) return -6;
   GPK_CHECK(gpk_launch_pad_copy(src_d, R, C, dst_d, RP, CP, (cudaStream_t)stream));
   return 0;
 }
 int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* C_d, int ldc, int M, int N, int K,
                 double alpha, int accumulate, int a_tri, int b_tri, int lower_only, void* stream) {
+  if (!A_d) return -1; if (!B_d) return -3; if (!C_d) return -5;
   if ((M % GPK_TILE) || (N % GPK_TILE) || (K % GPK_TILE)) return -7;
+  if (lda < K) return -2; if (ldb < K) return -4; if (ldc < N) return -6;
   GpkGemmArgs g{};
   g.A = A_d; g.lda = lda; g.B = B_d; g.ldb = ldb; g.C = C_d; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.alpha = alpha;
   g.accumulate = accumulate; g.a_tri = a_tri; g.b_tri = b_tri; g.lower_only = lower_only; g.epilogue = GPK_EPI_STORE;
@@ -281,6 +298,7 @@ int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* 
   return 0;
 }
 int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream) {
+  if (!sink_d) return -3;
   if (blocks < 0) {  // negative block count selects the m16n8k16 shape: 8 warps x 8 accumulators x 4096 flops
     GPK_CHECK(gpk_launch_dmma16816_probe(-blocks, iters, sink_d, (cudaStream_t)stream));
     if (flops_h) *flops_h = (double)(-blocks) * 8.0 * 8.0 * 4096.0 * (double)iters;
@@ -294,21 +312,23 @@ int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void*
 
 int gpk_gemv(const double* A_d, int lda, int M, int K, const double* v_d, int T, double* out_d, double alpha, double beta,
              int transpose, void* stream) {
-  if (!A_d) return -1; if (T < 1) return -6;
+  if (!A_d) return -1; if (!v_d) return -5; if (T < 1) return -6; if (!out_d) return -7;
   if (transpose) GPK_CHECK(gpk_launch_gemv_t(A_d, lda, M, K, v_d, T, out_d, alpha, (cudaStream_t)stream));
   else GPK_CHECK(gpk_launch_gemv_n(A_d, lda, M, K, v_d, T, out_d, alpha, beta, (cudaStream_t)stream));
   return 0;
 }
 int gpk_trimv(const double* M_d, int NP, const double* v_d, double* out_d, int T, int upper, void* stream) {
-  if (!M_d) return -1; if (T < 1) return -5;
+  if (!M_d) return -1; if (!v_d) return -3; if (!out_d) return -4; if (T < 1) return -5;
   GPK_CHECK(gpk_launch_trimv(M_d, NP, NP, v_d, T, out_d, T, upper, T, (cudaStream_t)stream));
   return 0;
 }
 int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pad_value, void* stream) {
+  if (!A_d) return -1; if (n < 0 || lda < n) return -2;
   GPK_CHECK(gpk_launch_fix_diag(A_d, lda, n, n_valid, add, pad_value, (cudaStream_t)stream));
   return 0;
 }
 int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream) {
+  if (!A_d) return -1; if (!sum_d) return -4;
   GPK_CHECK(gpk_launch_logdiag(A_d, lda, n, sum_d, (cudaStream_t)stream));
   return 0;
 }
