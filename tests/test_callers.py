@@ -138,3 +138,12 @@ def test_stacked_predict_is_bit_identical_to_the_member_loop(rows):
     got_m = gpr.predict_stacked(models, Xs, return_std=False)
     for gm, (wm, _) in zip(got_m, want):
         np.testing.assert_array_equal(gm, wm)
+
+
+@pytest.mark.gpu
+def test_trainer_mirror_matches_the_reference_trainer_on_device(golden_dir, tmp_path):
+    """callers.GPTrainer through libgpk.so against the golden made by the reference's own GPTrainer.train_gp_models
+    (gp_trainer.py:121-205; oracle/make_golden_trainer.py): six ARD fits with 3 restarts each, held-out scores through
+    the stacked predict, schema-B pickle round trip."""
+    from _trainer_check import check_trainer_against_reference
+    check_trainer_against_reference(golden_dir, tmp_path)

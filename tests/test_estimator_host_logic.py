@@ -316,3 +316,24 @@ def test_per_output_members_with_scalers_match_the_reference_loop():
     np.testing.assert_allclose(mean2, mean, rtol=1e-12, atol=1e-14)
     with pytest.raises(ValueError):
         pg.predict_batch(np.full((2, 5), np.nan))
+
+
+from _trainer_check import check_trainer_against_reference as _check_trainer_against_reference  # noqa: E402
+
+
+def test_trainer_mirror_matches_the_reference_trainer(golden_dir, tmp_path):
+    z, tr = _check_trainer_against_reference(golden_dir, tmp_path)
+    # vectorised npz ingest == the reference's per-sample loop (gp_trainer.py:48-103) on the same flight files
+    os_ = __import__("os")
+    os_.makedirs(tr.data_dir, exist_ok=True)
+    for j in (0, 1):
+        np.savez(os_.path.join(tr.data_dir, f"flight_data_{j}.npz"), states_prev=z[f"flight{j}_prev"],
+                 controls=z[f"flight{j}_ctrl"], states_next=z[f"flight{j}_next"], dt_values=z[f"flight{j}_dt"])
+    X, y = tr.load_training_data()
+    order = np.lexsort(X.T[::-1])
+    np.testing.assert_array_equal(X[order], z["ingest_X"])
+    np.testing.assert_allclose(y[order], z["ingest_y"], rtol=0, atol=1e-15)
+    Xs, ys = tr.load_training_data(max_samples=10)
+    assert Xs.shape == (10, 10) and ys.shape == (10, 6)
+    with pytest.raises(FileNotFoundError):
+        type(tr)(data_dir=str(tmp_path / "none"), model_dir=str(tmp_path / "models")).load_training_data()

@@ -92,3 +92,62 @@ def test_shard_helpers_single_process():
     assert parallel.shard_indices(10, 1, 4) == [1, 5, 9]
     assert [parallel.row_block(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 8), (8, 10)]
     assert parallel.run_sharded(lambda v: v * 2, [1, 2, 3]) == [2, 4, 6]
+
+
+def _trainer_case():
+    rng = np.random.default_rng(4)
+    X = rng.standard_normal((70, 4)) * np.array([1.0, 3.0, 0.5, 2.0])
+    Y = np.stack([np.sin(X[:, 0]), np.cos(X[:, 1] / 3), X[:, 2] * X[:, 3]], 1) + 0.05 * rng.standard_normal((70, 3))
+    return X, Y
+
+
+def _run_trainer(tmp):
+    """callers.GPTrainer with the oracle-backed engine double (no GPU here); stats + one prediction per component"""
+    import warnings
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_estimator_host_logic import OracleEngine
+    from unmanned_aerial_vehicles_b200 import callers, gpr as gpr_mod
+    real, gpr_mod.DeviceGP = gpr_mod.DeviceGP, OracleEngine
+    try:
+        X, Y = _trainer_case()
+        tr = callers.GPTrainer(data_dir=os.path.join(tmp, "d"), model_dir=os.path.join(tmp, "m"), random_state=0)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            stats = tr.train_gp_models(X, Y)
+        pg = callers.PerOutputGP(tr.gp_models, tr.scalers_X, tr.scalers_y, names=list(stats))
+        mean, std = pg.predict_batch(X[:4] + 0.01)
+    finally:
+        gpr_mod.DeviceGP = real
+    return {n: (s["log_marginal_likelihood"], s["rmse"], s["kernel"]) for n, s in stats.items()}, mean.tolist(), std.tolist()
+
+
+def _trainer_worker(rank, world, port, q, tmp):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    q.put((rank,) + _run_trainer(os.path.join(tmp, str(rank))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_trainer_components_sharded_over_two_ranks_equal_the_serial_loop(tmp_path):
+    """gp_trainer.py:140-176: the per-component fits are independent; sharded over 2 ranks (component i -> rank i % 2,
+    fitted models pickled to the other rank as host NumPy) every rank must hold the serial loop's models and scores."""
+    sys.path.insert(0, ROOT)
+    serial = _run_trainer(str(tmp_path / "serial"))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_trainer_worker, args=(r, 2, port, q, str(tmp_path))) for r in range(2)]
+    [p.start() for p in procs]
+    outs = sorted(q.get(timeout=300) for _ in range(2))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for out in outs:
+        assert out[1].keys() == serial[0].keys() and len(serial[0]) == 3
+        for n in serial[0]:
+            assert out[1][n][2] == serial[0][n][2]                                   # same kernel_ string
+            np.testing.assert_allclose(out[1][n][:2], serial[0][n][:2], rtol=1e-12)
+        np.testing.assert_allclose(out[2], serial[1], rtol=1e-10, atol=1e-13)
+        np.testing.assert_allclose(out[3], serial[2], rtol=1e-10, atol=1e-13)

@@ -5,6 +5,8 @@ reference's per-row API and adding the batched form the GPU wants.
   build_gp_residuals       <- src/px4/mpc.py:1475-1511          (25 sequential one-row predicts -> ONE batched call)
   PerOutputGP              <- src/px4/pretrained_gp.py:27-98, gp_trainer.py:207-227 (schema B: per-output models
                               + scalers), gp_enhanced_mpc.py:94-183 (schema C)
+  GPTrainer                <- src/px4/gp_trainer.py:27-245     (npz ingest, per-output scaler + ARD fit loop, test
+                              metrics, schema-B pickle); fits shard over ranks, test predictions are ONE device call
   adopt_pickle             <- the three pickle schemas of SURVEY section 5
   evaluate_residual_metrics<- src/px4/evaluate_gp_offline.py:186-312 (MSE/RMSE/R2/improvement/frac_better)
   load_csv_dataset         <- src/px4/train_gp_offline.py:22-76 (vectorised: no per-row Python loop)
@@ -243,6 +245,120 @@ class PerOutputGP:
         x = np.concatenate([np.asarray(state)[:6], np.asarray(control)[:4]]).reshape(1, -1)
         m, s = self.predict_batch(x)
         return m[0], s[0]
+
+
+OUTPUT_NAMES = ["x_residual", "y_residual", "z_residual", "vx_residual", "vy_residual", "vz_residual"]
+
+
+class GPTrainer:
+    """The reference's offline trainer (gp_trainer.py:27-245) with the same surface and the same schema-B pickle:
+    one StandardScaler pair + one ARD ``C(1, fixed) * RBF([1]*D, (0.1, 10)) + White(0.01, (1e-5, 10))`` model with
+    3 restarts per residual component, fitted on an 80/20 split (seed 42), scored on the held-out rows.
+
+    What differs underneath: the npz ingest is array arithmetic instead of a per-sample Python loop
+    (gp_trainer.py:71-91); the component fits are independent, so under torch.distributed they are sharded over the
+    ranks (parallel.run_sharded; every rank ends with every model); the held-out predictions of all components are
+    one device call.  ``random_state`` seeds the restart draws (the reference leaves them on NumPy's global stream)."""
+
+    def __init__(self, data_dir="data/training_data", model_dir="data/trained_models", random_state=None, group=None):
+        self.data_dir, self.model_dir = data_dir, model_dir
+        os.makedirs(model_dir, exist_ok=True)
+        self.gp_models, self.scalers_X, self.scalers_y, self.training_stats = {}, {}, {}, {}
+        self.random_state, self.group = random_state, group
+
+    @staticmethod
+    def _nominal_dynamics(state, control, dt):
+        """double integrator (gp_trainer.py:105-119); accepts one sample or stacked samples with dt of shape (n,)"""
+        state, control = np.asarray(state, dtype=np.float64), np.asarray(control, dtype=np.float64)
+        dt = np.asarray(dt, dtype=np.float64)[..., None] if np.ndim(dt) else dt
+        return np.concatenate([state[..., :3] + state[..., 3:6] * dt, state[..., 3:6] + control[..., :3] * dt], axis=-1)
+
+    def load_training_data(self, max_samples=None):
+        """every flight_data_*.npz under data_dir -> X (n, 10) = [state_prev, control], y (n, 6) = residual"""
+        import glob
+
+        files = glob.glob(os.path.join(self.data_dir, "flight_data_*.npz"))
+        if not files:
+            raise FileNotFoundError(f"No training data found in {self.data_dir}")
+        Xs, ys = [], []
+        for f in files:
+            d = np.load(f)
+            prev, ctrl = np.asarray(d["states_prev"], dtype=np.float64), np.asarray(d["controls"], dtype=np.float64)
+            if len(prev) == 0:
+                continue
+            ys.append(np.asarray(d["states_next"], dtype=np.float64) - self._nominal_dynamics(prev, ctrl, d["dt_values"]))
+            Xs.append(np.hstack([prev, ctrl]))
+        X = np.vstack(Xs) if Xs else np.empty((0, 10))
+        y = np.vstack(ys) if ys else np.empty((0, 6))
+        if max_samples and len(X) > max_samples:
+            idx = np.random.choice(len(X), max_samples, replace=False)            # gp_trainer.py:97-100
+            X, y = X[idx], y[idx]
+        return X, y
+
+    def _make_estimator(self, n_features, t):
+        from sklearn.gaussian_process.kernels import ConstantKernel
+
+        kernel = ConstantKernel(1.0, constant_value_bounds="fixed") * RBF(
+            length_scale=[1.0] * n_features, length_scale_bounds=(0.1, 10.0)) + WhiteKernel(
+            noise_level=0.01, noise_level_bounds=(1e-5, 1e1))                      # gp_trainer.py:163-166
+        return GaussianProcessRegressor(kernel=kernel, n_restarts_optimizer=3, alpha=1e-6, normalize_y=False,
+                                        random_state=self.random_state)
+
+    def train_gp_models(self, X, y, test_size=0.2):
+        from sklearn.model_selection import train_test_split
+        from sklearn.preprocessing import StandardScaler
+
+        from .parallel import run_sharded
+
+        X, y = np.asarray(X, dtype=np.float64), np.asarray(y, dtype=np.float64)
+        X_train, X_test, y_train, y_test = train_test_split(X, y, test_size=test_size, random_state=42)
+        todo = [(i, name) for i, name in enumerate(OUTPUT_NAMES[: y.shape[1]]) if np.std(y_train[:, i]) >= 1e-6]
+
+        def fit_one(item):
+            i, name = item
+            sX, sY = StandardScaler(), StandardScaler()
+            Xs = sX.fit_transform(X_train)
+            ys = sY.fit_transform(y_train[:, i].reshape(-1, 1)).flatten()
+            return sX, sY, self._make_estimator(X.shape[1], i).fit(Xs, ys)
+
+        fitted = run_sharded(fit_one, todo, self.group)     # pickled across ranks as host NumPy, refactored lazily
+        for (i, name), (sX, sY, gp) in zip(todo, fitted):
+            self.gp_models[name], self.scalers_X[name], self.scalers_y[name] = gp, sX, sY
+        results = {}
+        if todo:
+            members = PerOutputGP({n: self.gp_models[n] for _, n in todo}, self.scalers_X, self.scalers_y,
+                                  names=[n for _, n in todo])
+            pred, _ = members.predict_batch(X_test, return_std=False)             # all components, one device call
+            for k, (i, name) in enumerate(todo):
+                gp, t = self.gp_models[name], y_test[:, i]
+                mse = float(np.mean((t - pred[:, k]) ** 2))
+                ss_tot = float(np.sum((t - t.mean()) ** 2))
+                r2 = 1.0 - float(np.sum((t - pred[:, k]) ** 2)) / ss_tot if ss_tot > 0 else float("nan")
+                results[name] = {"mse": mse, "rmse": float(np.sqrt(mse)), "r2": r2, "kernel": str(gp.kernel_),
+                                 "log_marginal_likelihood": gp.log_marginal_likelihood()}
+        self.training_stats = results
+        return results
+
+    def save_models(self, model_name=None):
+        import time
+        from datetime import datetime
+
+        if model_name is None:
+            model_name = f"gp_model_{datetime.now().strftime('%Y%m%d_%H%M%S')}"
+        path = os.path.join(self.model_dir, f"{model_name}.pkl")
+        with open(path, "wb") as f:                                               # schema B (gp_trainer.py:214-221)
+            pickle.dump({"gp_models": self.gp_models, "scalers_X": self.scalers_X, "scalers_y": self.scalers_y,
+                         "training_stats": self.training_stats, "model_name": model_name,
+                         "creation_time": time.time()}, f)
+        return path
+
+    def load_models(self, model_path):
+        with open(model_path, "rb") as f:
+            data = pickle.load(f)
+        self.gp_models = {k: _to_b200(v) for k, v in data["gp_models"].items()}
+        self.scalers_X, self.scalers_y = data["scalers_X"], data["scalers_y"]
+        self.training_stats = data["training_stats"]
+        return self.training_stats
 
 
 def adopt_pickle(obj):
