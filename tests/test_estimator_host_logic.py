@@ -337,3 +337,92 @@ def test_trainer_mirror_matches_the_reference_trainer(golden_dir, tmp_path):
     assert Xs.shape == (10, 10) and ys.shape == (10, 6)
     with pytest.raises(FileNotFoundError):
         type(tr)(data_dir=str(tmp_path / "none"), model_dir=str(tmp_path / "models")).load_training_data()
+
+
+def _schema_pickles(tmp_path, drop=None):
+    """schema-B and schema-C pickles with stock-sklearn members (fixed theta), as gp_trainer.py:214-221 writes them"""
+    from sklearn.preprocessing import StandardScaler
+
+    rng = np.random.default_rng(21)
+    X = rng.standard_normal((90, 10)) * np.linspace(0.5, 3.0, 10) + np.linspace(-1, 1, 10)
+    Y = np.stack([np.sin(X[:, i]) + 0.3 * X[:, (i + 3) % 10] for i in range(6)], 1) + 0.05 * rng.standard_normal((90, 6))
+    namesB = ["x_residual", "y_residual", "z_residual", "vx_residual", "vy_residual", "vz_residual"]
+    namesC = ["pos_x", "pos_y", "pos_z", "vel_vx", "vel_vy", "vel_vz"]
+    models, sX, sY = {}, {}, {}
+    for i, n in enumerate(namesB):
+        if drop and n in drop:
+            continue
+        sX[n], sY[n] = StandardScaler().fit(X), StandardScaler().fit(Y[:, i:i + 1])
+        k = CK(1.0, constant_value_bounds="fixed") * RBF(np.linspace(0.8, 2.0, 10) + 0.1 * i, (0.1, 10)) + WhiteKernel(0.02 + 0.01 * i, (1e-5, 10))
+        models[n] = SkGPR(kernel=k, alpha=1e-6, optimizer=None).fit(sX[n].transform(X), sY[n].transform(Y[:, i:i + 1]).ravel())
+    pB = tmp_path / "b.pkl"
+    pickle.dump({"gp_models": models, "scalers_X": sX, "scalers_y": sY, "training_stats": {"note": 1}}, open(pB, "wb"))
+    pC = tmp_path / "c.pkl"
+    b2c = dict(zip(namesB, namesC))
+    pickle.dump({"models": {b2c[n]: m for n, m in models.items()}, "scalers_input": {b2c[n]: s for n, s in sX.items()},
+                 "scalers_output": {b2c[n]: s for n, s in sY.items()}}, open(pC, "wb"))
+    return X, str(pB), str(pC), models, sX, sY, namesB
+
+
+def test_pretrained_loader_equals_the_reference_class(tmp_path):
+    """callers.PreTrainedGP against the reference's own PreTrainedGP (src/px4/pretrained_gp.py, imported unmodified
+    when the reference tree is present -- build container only) and against its loop restated with stock sklearn."""
+    import os
+    import sys
+
+    from unmanned_aerial_vehicles_b200 import callers
+
+    X, pB, _, models, sX, sY, names = _schema_pickles(tmp_path, drop={"z_residual"})
+    mine = callers.PreTrainedGP(pB)
+    assert mine.is_loaded and mine.get_stats()["available_models"] == [n for n in names if n != "z_residual"]
+    rows = [(X[i, :6] + 0.01, X[i, 6:] - 0.01) for i in (0, 7, 33)]
+    ref = None
+    if os.path.exists("/root/reference/src/px4/pretrained_gp.py"):
+        sys.path.insert(0, "/root/reference/src/px4")
+        try:
+            import pretrained_gp
+            ref = pretrained_gp.PreTrainedGP(pB)
+        finally:
+            sys.path.remove("/root/reference/src/px4")
+    for st, ct in rows:
+        m, s = mine.predict_residual(st, ct)
+        x = np.concatenate([st, ct]).reshape(1, -1)
+        for i, n in enumerate(names):
+            if n not in models:
+                assert m[i] == 0.0 and s[i] == 1e6
+                continue
+            ms, ss = models[n].predict(sX[n].transform(x), return_std=True)
+            np.testing.assert_allclose(m[i], sY[n].inverse_transform(ms.reshape(-1, 1)).ravel()[0], rtol=1e-6, atol=1e-9)
+            np.testing.assert_allclose(s[i], abs(ss[0] * sY[n].scale_[0]), rtol=0, atol=1e-8)
+        if ref is not None:
+            rm, rs = ref.predict_residual(st, ct)
+            np.testing.assert_allclose(m, rm, rtol=1e-6, atol=1e-9)
+            np.testing.assert_allclose(s, rs, rtol=0, atol=1e-8)
+            assert abs(mine.get_uncertainty(st, ct) - ref.get_uncertainty(st, ct)) <= 1e-8 * 1e6
+    mb, sb = mine.predict_residual_batch(np.array([r[0] for r in rows]), np.array([r[1] for r in rows]))
+    np.testing.assert_allclose(mb[1], mine.predict_residual(*rows[1])[0], rtol=1e-12, atol=1e-14)
+    missing = callers.PreTrainedGP(str(tmp_path / "nope.pkl"))
+    m, s = missing.predict_residual(*rows[0])
+    assert not missing.is_loaded and not m.any() and (s == 1e6).all()
+
+
+def test_enhanced_mpc_residuals_follow_the_reference_loop(tmp_path):
+    """callers.EnhancedMPCResiduals = gp_enhanced_mpc.py:142-183 (rclpy node, not importable here): 12-d state, input
+    through pos_x's scaler for every member, mean only, zeros when no complete model set is loaded."""
+    from unmanned_aerial_vehicles_b200 import callers
+
+    X, _, pC, models, sX, sY, namesB = _schema_pickles(tmp_path)
+    g = callers.EnhancedMPCResiduals(pC)
+    assert g.gp_available
+    state = np.concatenate([X[3, :3], [9.0, 9.0, 9.0], X[3, 3:6], [7.0, 7.0, 7.0]])   # attitude slots are ignored
+    control = X[3, 6:]
+    pos, vel = g.predict_gp_residuals(state, control)
+    xin = sX["x_residual"].transform(np.concatenate([state[:3], state[6:9], control]).reshape(1, -1))
+    want = [sY[n].inverse_transform(models[n].predict(xin).reshape(-1, 1)).ravel()[0] for n in namesB]
+    np.testing.assert_allclose(np.concatenate([pos, vel]), want, rtol=1e-6, atol=1e-9)
+    P, V = g.predict_gp_residuals_batch(np.tile(state, (4, 1)), np.tile(control, (4, 1)))
+    assert P.shape == (4, 3) and V.shape == (4, 3)
+    np.testing.assert_allclose(P[2], pos, rtol=1e-12, atol=1e-14)
+    _, _, pC2, *_ = _schema_pickles(tmp_path, drop={"vy_residual"})
+    g2 = callers.EnhancedMPCResiduals(pC2)
+    assert not g2.gp_available and not np.any(g2.predict_gp_residuals(state, control))

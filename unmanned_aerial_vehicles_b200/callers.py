@@ -5,6 +5,8 @@ reference's per-row API and adding the batched form the GPU wants.
   build_gp_residuals       <- src/px4/mpc.py:1475-1511          (25 sequential one-row predicts -> ONE batched call)
   PerOutputGP              <- src/px4/pretrained_gp.py:27-98, gp_trainer.py:207-227 (schema B: per-output models
                               + scalers), gp_enhanced_mpc.py:94-183 (schema C)
+  PreTrainedGP             <- src/px4/pretrained_gp.py:12-118   (schema-B loader with the per-row API of the controller)
+  EnhancedMPCResiduals     <- src/px4/gp_enhanced_mpc.py:94-183 (schema-C loader: pos_*/vel_* members, mean only)
   GPTrainer                <- src/px4/gp_trainer.py:27-245     (npz ingest, per-output scaler + ARD fit loop, test
                               metrics, schema-B pickle); fits shard over ranks, test predictions are ONE device call
   adopt_pickle             <- the three pickle schemas of SURVEY section 5
@@ -245,6 +247,109 @@ class PerOutputGP:
         x = np.concatenate([np.asarray(state)[:6], np.asarray(control)[:4]]).reshape(1, -1)
         m, s = self.predict_batch(x)
         return m[0], s[0]
+
+
+class PreTrainedGP:
+    """pretrained_gp.py:12-118 with the same surface: loads a schema-B pickle at construction, one-row
+    ``predict_residual`` -> (mean (6,), std (6,)), missing components (0, 1e6), everything (0, 1e6) when nothing is
+    loaded.  The six members answer in one device call; ``predict_residual_batch`` is the horizon form."""
+
+    def __init__(self, model_path):
+        self.model_path = model_path
+        self.gp_models, self.scalers_X, self.scalers_y, self.training_stats = {}, {}, {}, {}
+        self.is_loaded = False
+        self._members = None
+        self.load_models()
+
+    def load_models(self):
+        if not os.path.exists(self.model_path):
+            return False
+        try:
+            with open(self.model_path, "rb") as f:
+                data = pickle.load(f)
+            members = PerOutputGP(data["gp_models"], data["scalers_X"], data["scalers_y"], names=OUTPUT_NAMES)
+            self.training_stats = data["training_stats"]
+        except Exception as e:  # the reference reports and carries on without a model (pretrained_gp.py:48-50)
+            print(f"Failed to load GP models: {e}")
+            return False
+        self._members = members
+        self.gp_models, self.scalers_X, self.scalers_y = members.models, members.scalers_X, members.scalers_y
+        self.is_loaded = True
+        return True
+
+    def predict_residual_batch(self, states, controls):
+        """(M, >=6), (M, >=4) -> mean (M, 6), std (M, 6)"""
+        states, controls = np.atleast_2d(np.asarray(states, dtype=np.float64)), np.atleast_2d(np.asarray(controls, dtype=np.float64))
+        if not self.is_loaded:
+            return np.zeros((len(states), 6)), np.full((len(states), 6), 1e6)
+        try:
+            return self._members.predict_batch(np.hstack([states[:, :6], controls[:, :4]]))
+        except Exception as e:  # pretrained_gp.py:91-94: a failed prediction answers (0, 1e6)
+            print(f"GP prediction failed: {e}")
+            return np.zeros((len(states), 6)), np.full((len(states), 6), 1e6)
+
+    def predict_residual(self, state, control):
+        m, s = self.predict_residual_batch(np.asarray(state)[None, :], np.asarray(control)[None, :])
+        return m[0], s[0]
+
+    def get_uncertainty(self, state, control):
+        return float(np.mean(self.predict_residual(state, control)[1]))
+
+    def get_stats(self):
+        return {"is_loaded": self.is_loaded, "model_path": self.model_path,
+                "available_models": list(self.gp_models.keys()), "training_stats": self.training_stats}
+
+
+class EnhancedMPCResiduals:
+    """The GP part of gp_enhanced_mpc.py (:94-183) without the ROS node around it: schema-C pickle
+    (``models`` / ``scalers_input`` / ``scalers_output`` keyed pos_x..vel_vz, all six required), 12-d MPC state of
+    which [0:3] and [6:9] are position and velocity, mean only, ``(zeros(3), zeros(3))`` when unavailable.  Like the
+    reference, every member sees the input through the scaler of ``pos_x`` (:160)."""
+
+    REQUIRED = ["pos_x", "pos_y", "pos_z", "vel_vx", "vel_vy", "vel_vz"]
+
+    def __init__(self, model_file=None):
+        self.gp_available = False
+        self.gp_predictions_enabled = False
+        self.training_stats = {}
+        self._members = None
+        if model_file:
+            self.setup_gp(model_file)
+
+    def setup_gp(self, model_file):
+        if not model_file or not os.path.exists(model_file):
+            return False
+        try:
+            with open(model_file, "rb") as f:
+                pkg = pickle.load(f)
+            if not all(k in pkg["models"] for k in self.REQUIRED):
+                raise ValueError("Incomplete GP model set")
+            shared = {k: pkg["scalers_input"]["pos_x"] for k in self.REQUIRED}
+            self._members = PerOutputGP({k: pkg["models"][k] for k in self.REQUIRED}, shared, pkg["scalers_output"],
+                                        names=self.REQUIRED)
+            self.training_stats = pkg.get("training_stats", {})
+        except Exception as e:
+            print(f"Failed to load GP models: {e}")
+            return False
+        self.gp_available = self.gp_predictions_enabled = True
+        return True
+
+    def predict_gp_residuals_batch(self, states, controls):
+        """(M, >=9), (M, 4) -> position residuals (M, 3), velocity residuals (M, 3): one device call"""
+        states, controls = np.atleast_2d(np.asarray(states, dtype=np.float64)), np.atleast_2d(np.asarray(controls, dtype=np.float64))
+        if not self.gp_available or not self.gp_predictions_enabled:
+            return np.zeros((len(states), 3)), np.zeros((len(states), 3))
+        try:
+            x = np.hstack([states[:, :3], states[:, 6:9], controls])
+            mean, _ = self._members.predict_batch(x, return_std=False)
+            return mean[:, :3], mean[:, 3:]
+        except Exception as e:
+            print(f"GP prediction failed: {e}")
+            return np.zeros((len(states), 3)), np.zeros((len(states), 3))
+
+    def predict_gp_residuals(self, state, control):
+        p, v = self.predict_gp_residuals_batch(np.asarray(state)[None, :], np.asarray(control)[None, :])
+        return p[0], v[0]
 
 
 OUTPUT_NAMES = ["x_residual", "y_residual", "z_residual", "vx_residual", "vy_residual", "vz_residual"]
