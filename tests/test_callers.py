@@ -147,3 +147,26 @@ def test_trainer_mirror_matches_the_reference_trainer_on_device(golden_dir, tmp_
     the stacked predict, schema-B pickle round trip."""
     from _trainer_check import check_trainer_against_reference
     check_trainer_against_reference(golden_dir, tmp_path)
+
+
+@pytest.mark.gpu
+def test_offline_flow_on_device_reaches_the_reference_optimum(golden_dir, tmp_path):
+    """train_gp_offline.py flow -> schema-A pickle -> evaluate_gp_offline.py flow through libgpk.so on the reference's
+    CSV rows: theta* and LML of the golden made by the reference's own SimpleQuadrotorGP.train_gp (seed injected)."""
+    import warnings
+    from unmanned_aerial_vehicles_b200 import offline
+    z = np.load(os.path.join(golden_dir, "simple_gp_csv.npz"))
+    gp = callers.SimpleQuadrotorGP(max_data_points=10000)
+    gp.extend(z["X"], z["Y"])
+    (tmp_path / "data").mkdir()
+    gp.save_dataset(str(tmp_path / "data" / "gp_mpc_data_a.csv"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        path = offline.train_offline(str(tmp_path / "data"), str(tmp_path / "models"), random_state=0)
+    model = offline.load_gp_model(path)
+    np.testing.assert_allclose(model.kernel_.theta, z["theta"], rtol=0, atol=1e-4)
+    assert abs(model.log_marginal_likelihood_value_ - float(z["lml"])) <= 1e-6 * abs(float(z["lml"]))
+    df, X_feat, R_true, X_state, U_ctrl = offline.load_dataset(tmp_path / "data" / "gp_mpc_data_a.csv")
+    out = offline.evaluate_gp(model, X_feat, R_true, X_state, U_ctrl, save_prefix=tmp_path / "run")
+    assert out["global"]["mse_gp"] < out["global"]["mse_nom"] and os.path.exists(tmp_path / "run_metrics.csv")
+    np.testing.assert_allclose(out["per_component"]["mse_nom"], np.mean(R_true ** 2, axis=0), rtol=1e-9)
