@@ -169,3 +169,37 @@ def test_offline_training_flow_and_evaluation_round_trip(golden_dir, tmp_path):
         p = tmp_path / "bad.pkl"; pickle.dump({"gp_model": 3}, open(p, "wb")); offline.load_gp_model(p)
     with pytest.raises(ValueError):
         offline.load_dataset(tmp_path / "data" / "broken.csv")
+
+
+def test_dataset_csv_is_written_like_the_reference_writes_it(tmp_path):
+    """SimpleQuadrotorGP.save_dataset (simple_gp.py:75-115): header, '%.18e' rows, append mode; byte-identical to the
+    reference's own method where the reference tree is present; the row filters of add_training_data (:118-141) agree."""
+    rng = np.random.default_rng(8)
+    mine = callers.SimpleQuadrotorGP(max_data_points=50)
+    ref = _ref("simple_gp").SimpleQuadrotorGP(max_data_points=50) if HAVE_REF else None
+    for i in range(40):
+        s = rng.standard_normal(6) * np.array([1, 1, 1, 2.5, 2.5, 2.5])
+        u = rng.standard_normal(4) * 1.5
+        nxt = s + 0.02 * np.concatenate([s[3:], u[:3]]) + rng.standard_normal(6) * 0.7
+        mine.add_training_data(s, u, nxt, 0.02)
+        if ref is not None:
+            ref.add_training_data(s, u, nxt, 0.02)
+    assert 0 < len(mine.X_train) < 40                                     # some rows fail each filter
+    a = tmp_path / "sub" / "mine.csv"
+    mine.save_dataset(str(a))
+    mine.save_dataset(str(a), overwrite=False)                             # appended without a second header
+    lines = open(a).read().splitlines()
+    assert lines[0] == "x,y,z,vx,vy,vz,ax,ay,az,yaw_rate,res_dx,res_dy,res_dz,res_dvx,res_dvy,res_dvz"
+    assert len(lines) == 1 + 2 * len(mine.X_train)
+    X, Y = callers.load_csv_dataset(a)
+    np.testing.assert_allclose(X[: len(mine.X_train)], np.array(mine.X_train), rtol=1e-14)   # pandas' fast float parser
+    mine.save_dataset(str(tmp_path / "nohdr.csv"), include_header=False)
+    assert len(open(tmp_path / "nohdr.csv").read().splitlines()) == len(mine.X_train)
+    callers.SimpleQuadrotorGP().save_dataset(str(tmp_path / "empty.csv"))
+    assert not os.path.exists(tmp_path / "empty.csv")
+    if ref is not None:
+        assert len(ref.X_train) == len(mine.X_train)
+        np.testing.assert_array_equal(np.array(ref.Y_train), np.array(mine.Y_train))
+        b = tmp_path / "ref.csv"
+        ref.save_dataset(str(b)); ref.save_dataset(str(b), overwrite=False)
+        assert open(a, "rb").read() == open(b, "rb").read()

@@ -79,12 +79,25 @@ class SimpleQuadrotorGP:
             self.X_train.append(np.asarray(xi, dtype=np.float64))
             self.Y_train.append(np.asarray(yi, dtype=np.float64))
 
-    def save_dataset(self, path):
-        import pandas as pd
+    def _to_numpy(self):
+        if len(self.X_train) == 0:
+            return np.empty((0, 10)), np.empty((0, 6))
+        return np.array(self.X_train), np.array(self.Y_train)
 
-        X = np.array(self.X_train) if len(self.X_train) else np.empty((0, 10))
-        Y = np.array(self.Y_train) if len(self.Y_train) else np.empty((0, 6))
-        pd.DataFrame(np.hstack([X, Y]), columns=FEATURE_COLS + RESIDUAL_COLS).to_csv(path, index=False)
+    def save_dataset(self, csv_path, include_header=True, overwrite=True):
+        """simple_gp.py:75-115: the 16-column CSV (np.savetxt, '%.18e'), appended without header when
+        ``overwrite=False`` and the file exists; nothing is written for an empty store."""
+        X, Y = self._to_numpy()
+        if X.shape[0] == 0:
+            return
+        data = np.hstack([X, Y])
+        os.makedirs(os.path.dirname(csv_path) or ".", exist_ok=True)
+        if overwrite or not os.path.exists(csv_path):
+            np.savetxt(csv_path, data, delimiter=",", header=",".join(FEATURE_COLS + RESIDUAL_COLS) if include_header else "",
+                       comments="")
+        else:
+            with open(csv_path, "ab") as f:
+                np.savetxt(f, data, delimiter=",")
 
     # -- train / predict -------------------------------------------------------------------------
     def train_gp(self):
