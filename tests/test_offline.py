@@ -203,3 +203,36 @@ def test_dataset_csv_is_written_like_the_reference_writes_it(tmp_path):
         b = tmp_path / "ref.csv"
         ref.save_dataset(str(b)); ref.save_dataset(str(b), overwrite=False)
         assert open(a, "rb").read() == open(b, "rb").read()
+
+
+def test_wrapper_error_behaviour_follows_the_reference(tmp_path):
+    """simple_gp.py:50-73 / :187-201: load_model answers False for a missing file, a pickle without 'gp_model' and a
+    corrupt file; predict_residual answers (zeros, ones) when the estimator raises -- but never hides a missing
+    CUDA library."""
+    from unmanned_aerial_vehicles_b200 import GpkUnavailable
+    gp = callers.SimpleQuadrotorGP()
+    assert gp.load_model(str(tmp_path / "none.pkl")) is False
+    pickle.dump({"model": 1}, open(tmp_path / "nokey.pkl", "wb"))
+    assert gp.load_model(str(tmp_path / "nokey.pkl")) is False
+    open(tmp_path / "corrupt.pkl", "wb").write(b"not a pickle")
+    assert gp.load_model(str(tmp_path / "corrupt.pkl")) is False and not gp.is_trained
+
+    class Raises:
+        def __init__(self, exc): self.exc = exc
+        def predict(self, X, return_std=False): raise self.exc
+
+    pickle.dump({"gp_model": 5, "training_count": 3}, open(tmp_path / "odd.pkl", "wb"))
+    assert gp.load_model(str(tmp_path / "odd.pkl")) is True and gp.training_count == 3   # the reference does not validate either
+    gp.gp_model = Raises(ValueError("X has 9 features"))
+    m, v = gp.predict_residual(np.zeros(6), np.zeros(4))
+    assert not m.any() and (v == 1).all() and gp.prediction_count == 0
+    gp.gp_model = Raises(GpkUnavailable("libgpk.so not found"))
+    with pytest.raises(GpkUnavailable):
+        gp.predict_residual(np.zeros(6), np.zeros(4))
+    if HAVE_REF:
+        rg = _ref("simple_gp").SimpleQuadrotorGP()
+        assert rg.load_model(str(tmp_path / "nokey.pkl")) is False and rg.load_model(str(tmp_path / "corrupt.pkl")) is False
+        assert rg.load_model(str(tmp_path / "odd.pkl")) is True and rg.training_count == 3
+        rg.gp_model = Raises(ValueError("x"))
+        rm, rv = rg.predict_residual(np.zeros(6), np.zeros(4))
+        np.testing.assert_array_equal(rm, m); np.testing.assert_array_equal(rv, v)

@@ -22,6 +22,7 @@ from collections import deque
 import numpy as np
 from sklearn.gaussian_process.kernels import RBF, WhiteKernel
 
+from . import _lib
 from .gpr import GaussianProcessRegressor, predict_stacked
 
 FEATURE_COLS = ["x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az", "yaw_rate"]
@@ -117,11 +118,18 @@ class SimpleQuadrotorGP:
             self.is_trained = False
 
     def predict_residual(self, state, control):
-        """one row -> (mean (6,), variance (6,)), as simple_gp.py:187-201"""
+        """one row -> (mean (6,), variance (6,)), as simple_gp.py:187-201: (zeros, ones) when untrained or when the
+        prediction raises (a missing CUDA library is not swallowed: there is no silent fallback)"""
         if not self.is_trained:
             return np.zeros(6), np.ones(6)
-        x = np.concatenate([state, control]).reshape(1, -1)
-        mean, std = self.gp_model.predict(x, return_std=True)
+        try:
+            x = np.concatenate([state, control]).reshape(1, -1)
+            mean, std = self.gp_model.predict(x, return_std=True)
+        except _lib.GpkUnavailable:
+            raise
+        except Exception as e:
+            print(f"GP prediction failed: {e}")
+            return np.zeros(6), np.ones(6)
         self.prediction_count += 1
         return mean.flatten(), std.flatten() ** 2
 
@@ -146,18 +154,21 @@ class SimpleQuadrotorGP:
         return self._nominal_dynamics(np.asarray(state)[:6], control, dt) + mean
 
     def load_model(self, model_path):
-        if not os.path.exists(model_path):
+        """simple_gp.py:50-73: schema-A pickle -> True; a missing file, a pickle without 'gp_model' or one that does
+        not load -> False (reported, not raised)"""
+        try:
+            if not os.path.exists(model_path):
+                return False
+            with open(model_path, "rb") as f:
+                data = pickle.load(f)
+            model = adopt_pickle({"gp_model": data["gp_model"]})
+            self.gp_model = model
+            self.is_trained = True
+            self.training_count = data.get("training_count", 0)
+            return True
+        except Exception as e:
+            print(f"Failed to load model: {e}")
             return False
-        with open(model_path, "rb") as f:
-            data = pickle.load(f)
-        model = adopt_pickle(data)
-        if isinstance(model, dict):
-            return False
-        self.gp_model = model
-        self.is_trained = True
-        if isinstance(data, dict):
-            self.training_count = data.get("training_count", 1)
-        return True
 
     def get_stats(self):
         return {"is_trained": self.is_trained, "data_points": len(self.X_train),
