@@ -236,3 +236,72 @@ def test_wrapper_error_behaviour_follows_the_reference(tmp_path):
         rg.gp_model = Raises(ValueError("x"))
         rm, rv = rg.predict_residual(np.zeros(6), np.zeros(4))
         np.testing.assert_array_equal(rm, m); np.testing.assert_array_equal(rv, v)
+
+
+def _ref_gp_evaluation():
+    """the reference's gp_evaluation.py imports matplotlib/seaborn at module level (absent here); only its model-facing
+    methods are exercised, so inert stand-ins for those two packages are enough to import it unmodified"""
+    from unittest import mock
+    stubs = {m: mock.MagicMock() for m in ("matplotlib", "matplotlib.pyplot", "seaborn")}
+    with mock.patch.dict(sys.modules, stubs):
+        return _ref("gp_evaluation")
+
+
+def test_model_evaluator_formats_generators_and_predictions(tmp_path):
+    """offline.GPModelEvaluator (gp_evaluation.py:53-330): both pickle formats, identity scalers when a multi-output
+    pickle has none, the seeded generators (array-equal to the reference's), prediction bands."""
+    from test_estimator_host_logic import _schema_pickles
+    X, pB, pC, models, sX, sY, namesB = _schema_pickles(tmp_path)
+    ev = offline.GPModelEvaluator(pC)
+    assert ev.mode == "multi" and list(ev.gp_models) == ["pos_x", "pos_y", "pos_z", "vel_vx", "vel_vy", "vel_vz"]
+    data = ev.generate_physical_test_data(50)
+    assert all(len(v) == 350 for v in data.values()) and list(data) == callers.FEATURE_COLS
+    pred = ev.predict_on_test_data(data)
+    Xt = np.column_stack([data[k] for k in callers.FEATURE_COLS])
+    for c_name, b_name in zip(ev.gp_models, namesB):
+        ms, ss = models[b_name].predict(sX[b_name].transform(Xt), return_std=True)
+        np.testing.assert_allclose(pred[c_name]["mean"], sY[b_name].inverse_transform(ms.reshape(-1, 1)).ravel(), rtol=1e-6, atol=1e-9)
+        np.testing.assert_allclose(pred[c_name]["std"], np.abs(ss * sY[b_name].scale_[0]), rtol=0, atol=1e-8)
+        np.testing.assert_array_equal(pred[c_name]["upper"], pred[c_name]["mean"] + 2 * pred[c_name]["std"])
+    # multi-output pickle without scalers -> identity scalers (gp_evaluation.py:92-102)
+    bare = tmp_path / "bare.pkl"
+    pickle.dump({"models": {"pos_x": models["x_residual"]}}, open(bare, "wb"))
+    evb = offline.GPModelEvaluator(str(bare))
+    ms, ss = models["x_residual"].predict(Xt, return_std=True)
+    np.testing.assert_allclose(evb.predict_on_test_data(data)["pos_x"]["mean"], ms, rtol=1e-6, atol=1e-9)
+    # single container (schema A), generic features when the model is not 10-dimensional
+    rng = np.random.default_rng(2)
+    Xs = rng.standard_normal((60, 4)); ys = np.sin(Xs[:, 0]) + 0.05 * rng.standard_normal(60)
+    single = SkGPR(kernel=RBF(1.0) + WhiteKernel(0.05), alpha=1e-6, optimizer=None).fit(Xs, ys)
+    pA = tmp_path / "a.pkl"
+    pickle.dump({"gp_model": single, "training_count": 2, "is_trained": True}, open(pA, "wb"))
+    eva = offline.GPModelEvaluator(str(pA))
+    assert eva.mode == "single" and eva.n_features == 4 and eva.training_stats["training_count"] == 2
+    gen = eva.generate_generic_test_data(30)
+    out = eva.predict_on_test_data(gen)["output"]
+    m1, s1 = single.predict(np.column_stack([gen[f"feature_{i}"] for i in range(4)]), return_std=True)
+    np.testing.assert_allclose(out["mean"], m1, rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(out["std"], s1, rtol=0, atol=1e-8)
+    for bad, exc in (({"other": 1}, KeyError), ({"gp_model": 3}, KeyError)):
+        pickle.dump(bad, open(tmp_path / "bad.pkl", "wb"))
+        with pytest.raises(exc):
+            offline.GPModelEvaluator(str(tmp_path / "bad.pkl"))
+    if HAVE_REF:
+        ref = _ref_gp_evaluation()
+        rev = ref.GPModelEvaluator(pC)
+        rdata = rev.generate_physical_test_data(50)
+        for k in data:
+            np.testing.assert_array_equal(data[k], rdata[k])
+        rpred = rev.predict_on_test_data(rdata)
+        for k in pred:
+            np.testing.assert_allclose(pred[k]["mean"], rpred[k]["mean"], rtol=1e-6, atol=1e-9)
+            np.testing.assert_allclose(pred[k]["std"], rpred[k]["std"], rtol=0, atol=1e-8)
+        ra = ref.GPModelEvaluator(str(pA))
+        assert (ra.mode, ra.n_features, ra.training_stats) == (eva.mode, eva.n_features, eva.training_stats)
+        rgen = ra.generate_generic_test_data(30)
+        for k in gen:
+            np.testing.assert_array_equal(gen[k], rgen[k])
+
+
+from sklearn.gaussian_process import GaussianProcessRegressor as SkGPR  # noqa: E402
+from sklearn.gaussian_process.kernels import RBF, WhiteKernel  # noqa: E402

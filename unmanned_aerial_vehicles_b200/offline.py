@@ -7,6 +7,8 @@ GP underneath is the B200 estimator.
   SimpleGPEnhancedMPC  <- src/px4/simple_gp.py:225-260         (uncertainty-gated use of the GP correction)
   f_nominal, load_gp_model, load_dataset, r2_score, evaluate_gp
                        <- src/px4/evaluate_gp_offline.py:49-365 (metrics dict + <prefix>_metrics.csv / .tex)
+  GPModelEvaluator     <- src/px4/gp_evaluation.py:40-330      (pickle-format detection, seeded test-data generators,
+                                                                  predict_on_test_data; the plotting half is out of scope)
   train_offline        <- src/px4/train_gp_offline.py:22-215    (CSV files -> SimpleQuadrotorGP.train_gp -> schema-A pickle
                                                                   + gp_model_latest.pkl link)
 """
@@ -21,7 +23,7 @@ from pathlib import Path
 
 import numpy as np
 
-from .callers import FEATURE_COLS, RESIDUAL_COLS, SimpleQuadrotorGP, adopt_pickle, load_csv_dataset
+from .callers import FEATURE_COLS, RESIDUAL_COLS, PerOutputGP, SimpleQuadrotorGP, _to_b200, adopt_pickle, load_csv_dataset
 
 COMPONENT_NAMES = ["dx", "dy", "dz", "dvx", "dvy", "dvz"]
 
@@ -241,3 +243,110 @@ def train_offline(data_dir, output_dir, model_name=None, pattern="*.csv", max_da
     except OSError as e:
         print(f"Could not create symlink: {e}")
     return path
+
+
+# ---------------------------------------------------------------------------------------- gp_evaluation.py
+class _IdentityScaler:
+    """gp_evaluation.py:40-50: what a multi-output pickle without scalers gets"""
+
+    def __init__(self):
+        self.scale_ = np.array([1.0])
+
+    def transform(self, X):
+        return X
+
+    def inverse_transform(self, X):
+        return X
+
+
+class GPModelEvaluator:
+    """The model-facing half of gp_evaluation.py (:53-330): format detection (``mode`` "multi" for a dict with
+    ``models`` [+ ``scalers_input`` / ``scalers_output``], "single" for a ``gp_model`` container), the seeded test-data
+    generators and ``predict_on_test_data`` with its mean / std / upper / lower bands.  All members of a multi-output
+    pickle answer in one device call.  Plots and the text report are not part of the path."""
+
+    def __init__(self, model_path):
+        self.model_path = model_path
+        self.mode = ""
+        self.gp_models, self.scalers_X, self.scalers_y = {}, {}, {}
+        self.gp_model, self.n_features = None, 0
+        self.training_stats, self.test_data = {}, {}
+        self.load_model()
+
+    def load_model(self):
+        with open(self.model_path, "rb") as f:
+            data = pickle.load(f)
+        if "models" in data:
+            self.mode = "multi"
+            self.gp_models = {k: _to_b200(v) for k, v in data["models"].items()}
+            self.scalers_X = data.get("scalers_input") or {k: _IdentityScaler() for k in self.gp_models}
+            self.scalers_y = data.get("scalers_output") or {k: _IdentityScaler() for k in self.gp_models}
+            self.training_stats = data.get("training_stats", {})
+            return
+        if "gp_model" in data:
+            gp_obj = data["gp_model"]
+            if not hasattr(gp_obj, "predict"):
+                raise KeyError("Unsupported gp_model type inside pickle")
+            self.mode = "single"
+            self.gp_model = _to_b200(gp_obj)
+            self.training_stats = {k: data.get(k) for k in ("training_count", "data_points_used", "timestamp", "is_trained")}
+            if hasattr(gp_obj, "n_features_in_"):
+                self.n_features = gp_obj.n_features_in_
+            elif hasattr(gp_obj, "X_train_"):
+                self.n_features = gp_obj.X_train_.shape[1]
+            else:
+                raise ValueError("gp_model has no 'n_features_in_' or 'X_train_'")
+            return
+        raise KeyError("Model file does not contain 'models' or 'gp_model'")
+
+    def generate_physical_test_data(self, n_samples=1000):
+        """gp_evaluation.py:150-207: n_samples uniform rows + 100 hover rows + a 200-row figure-8, drawn from NumPy's
+        global stream after ``np.random.seed(42)`` in the reference's order, so the arrays are the reference's."""
+        r = np.random
+        r.seed(42)
+        u = r.uniform
+        base = {"x": u(-10, 10, n_samples), "y": u(-10, 10, n_samples), "z": u(-2, 15, n_samples),
+                "vx": u(-5, 5, n_samples), "vy": u(-5, 5, n_samples), "vz": u(-3, 3, n_samples),
+                "ax": u(-8, 8, n_samples), "ay": u(-8, 8, n_samples), "az": u(1, 18, n_samples),
+                "yaw_rate": u(-1, 1, n_samples)}
+        pos = u(-5, 5, (100, 3))
+        hover = {"x": pos[:, 0], "y": pos[:, 1], "z": pos[:, 2] + 5.0}
+        for k, (m, sd) in (("vx", (0, 0.5)), ("vy", (0, 0.5)), ("vz", (0, 0.2)), ("ax", (0, 2)), ("ay", (0, 2)),
+                           ("az", (9.81, 1)), ("yaw_rate", (0, 0.3))):
+            hover[k] = r.normal(m, sd, 100)
+        t = np.linspace(0, 10, 200)
+        traj = {"x": 3 * np.sin(0.5 * t), "y": 3 * np.sin(t), "z": 5 + 2 * np.sin(0.3 * t),
+                "vx": 1.5 * np.cos(0.5 * t), "vy": 3.0 * np.cos(t), "vz": 0.6 * np.cos(0.3 * t)}
+        traj["ax"] = -0.75 * np.sin(0.5 * t) + r.normal(0, 1, 200)
+        traj["ay"] = -3.0 * np.sin(t) + r.normal(0, 1, 200)
+        traj["az"] = -0.18 * np.sin(0.3 * t) + 9.81 + r.normal(0, 0.5, 200)
+        traj["yaw_rate"] = r.normal(0, 0.2, 200)
+        return {k: np.concatenate([base[k], hover[k], traj[k]]) for k in base}
+
+    def generate_generic_test_data(self, n_samples=2000):
+        np.random.seed(42)
+        X = np.random.uniform(-1, 1, size=(n_samples, self.n_features))
+        return {f"feature_{i}": X[:, i] for i in range(self.n_features)}
+
+    @staticmethod
+    def _bands(mean, std):
+        std = np.abs(np.asarray(std).reshape(-1))
+        mean = np.asarray(mean).reshape(-1)
+        return {"mean": mean, "std": std, "upper": mean + 2 * std, "lower": mean - 2 * std}
+
+    def predict_on_test_data(self, test_data):
+        if self.mode == "multi":
+            X = np.column_stack([test_data[k] for k in FEATURE_COLS])
+            names = list(self.gp_models)
+            members = PerOutputGP(self.gp_models, {k: self.scalers_X.get(k, _IdentityScaler()) for k in names},
+                                  {k: self.scalers_y.get(k, _IdentityScaler()) for k in names}, names=names)
+            mean, std = members.predict_batch(X)
+            return {k: self._bands(mean[:, i], std[:, i]) for i, k in enumerate(names)}
+        if self.mode == "single":
+            if self.n_features == 10 and all(k in test_data for k in FEATURE_COLS):
+                X = np.column_stack([test_data[k] for k in FEATURE_COLS])
+            else:
+                X = np.column_stack([test_data[k] for k in sorted(k for k in test_data if k.startswith("feature_"))])
+            mean, std = self.gp_model.predict(X, return_std=True)
+            return {"output": self._bands(mean, std)}
+        return {}
