@@ -128,6 +128,23 @@ def _check(g, X, Y, ls, c, noise, jit):
     assert abs(g.lml() - lml) <= 1e-10 * abs(lml)
 
 
+def _check_predict(g, X, Y, ls, c, noise, jit):
+    """DistGP.predict against the oracle (sklearn _gpr.py:446-500): mean 1e-6 rel, std 1e-8 abs (north star), on
+    training rows (variance ~ noise: worst cancellation), nearby rows and far-field rows; ragged chunking"""
+    from oracle import gp_oracle as orc
+    rng = np.random.default_rng(9)
+    Xq = np.vstack([X[::37], X[3::41] + 1e-3 * rng.standard_normal(X[3::41].shape), 4.0 * rng.standard_normal((5, X.shape[1]))])
+    L, a = orc.factor(X, Y, ls, c, noise, jit)
+    m_o, s_o = orc.predict(Xq, X, L, a, ls, c, noise)
+    mean, std = g.predict(Xq, return_std=True, chunk_rows=128 if len(Xq) > 140 else 256)
+    assert mean.shape == (len(Xq), Y.shape[1]) and std.shape == mean.shape
+    np.testing.assert_allclose(mean, m_o, rtol=1e-6, atol=1e-9)
+    assert np.max(np.abs(std - s_o.reshape(len(Xq), -1))) <= 1e-8
+    np.testing.assert_allclose(g.predict(Xq[:7]), m_o[:7], rtol=1e-6, atol=1e-9)      # mean only: no exchange of W
+    with pytest.raises(ValueError):
+        g.predict(Xq[:, :-1])
+
+
 def test_single_rank_numpy_ops():
     from unmanned_aerial_vehicles_b200.dist_chol import DistGP, default_grid
     assert [default_grid(p) for p in (1, 2, 4, 6, 8)] == [(1, 1), (1, 2), (2, 2), (2, 3), (2, 4)]
@@ -139,6 +156,7 @@ def test_single_rank_numpy_ops():
     assert g.ops.log[:4] == ["side+", "side-", "join", "side+"] and g.ops.log[-1] == "join"
     g.solve()
     _check(g, X, Y, ls, c, noise, jit)
+    _check_predict(g, X, Y, ls, c, noise, jit)
     g2 = DistGP(X, Y, jit, NB=128, ops=NumpyOps(), lookahead=False)
     assert g2.factor(1.0 / ls, c, noise) == 0 and "side+" not in g2.ops.log
     g2.solve()
@@ -179,13 +197,14 @@ def _worker(rank, world, port, q, grid, n):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from test_dist_chol import NumpyOps, _check, _problem
+    from test_dist_chol import NumpyOps, _check, _check_predict, _problem
     from unmanned_aerial_vehicles_b200.dist_chol import DistGP
     X, Y, ls, c, noise, jit = _problem(n=n)
     g = DistGP(X, Y, jit, NB=128, ops=NumpyOps(dist), grid=grid)
     info = g.factor(1.0 / ls, c, noise)
     g.solve()
     _check(g, X, Y, ls, c, noise, jit)
+    _check_predict(g, X, Y, ls, c, noise, jit)
     bad = DistGP(np.zeros((300, 4)), Y[:300], 0.0, NB=128, ops=NumpyOps(dist), grid=grid)
     q.put((rank, info, g.owned, g.lml(), bad.factor(1.0 / ls, 1.0, 0.0)))
     dist.barrier(); dist.destroy_process_group()

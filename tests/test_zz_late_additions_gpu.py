@@ -69,3 +69,31 @@ def test_offline_flow_on_device_reaches_the_reference_optimum(golden_dir, tmp_pa
     out = offline.evaluate_gp(model, X_feat, R_true, X_state, U_ctrl, save_prefix=tmp_path / "run")
     assert out["global"]["mse_gp"] < out["global"]["mse_nom"] and os.path.exists(tmp_path / "run_metrics.csv")
     np.testing.assert_allclose(out["per_component"]["mse_nom"], np.mean(R_true ** 2, axis=0), rtol=1e-9)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,NB", [(1000, 256), (3000, 1024)])
+def test_distributed_factor_predicts_like_the_single_gpu_engine(n, NB):
+    """DistGP.predict (queries as one more row tile of the block-cyclic factor; every product a DMMA GEMM) on one
+    rank with the real CUDA ops against the single-GPU engine and the oracle: mean 1e-6 rel, std 1e-8 abs."""
+    from oracle import gp_oracle as orc
+    from unmanned_aerial_vehicles_b200.dist_chol import DistGP
+    from unmanned_aerial_vehicles_b200.engine import DeviceGP
+    rng = np.random.default_rng(1)
+    X = rng.standard_normal((n, 9)); Y = np.sin(X @ rng.standard_normal((9, 3)) / 3) + 0.1 * rng.standard_normal((n, 3))
+    ls = np.linspace(0.8, 2.0, 9)
+    Xq = np.vstack([X[::29], X[5::31] + 1e-3 * rng.standard_normal(X[5::31].shape), 4.0 * rng.standard_normal((7, 9))])
+    g = DistGP(X, Y, 1e-6, NB=NB)
+    assert g.factor(1.0 / ls, 1.0, 0.01) == 0
+    g.solve()
+    mean, std = g.predict(Xq, return_std=True, chunk_rows=128)
+    eng = DeviceGP(X, Y, 1e-6)
+    assert eng.factor(1.0 / ls, 1.0, 0.01) == 0
+    m_e, s_e, _, _ = eng.predict(Xq, np.zeros(3), np.ones(3), True)
+    np.testing.assert_allclose(mean, m_e, rtol=1e-6, atol=1e-9)
+    assert np.max(np.abs(std - s_e)) <= 1e-8
+    L, a = orc.factor(X, Y, ls, 1.0, 0.01, 1e-6)
+    m_o, s_o = orc.predict(Xq, X, L, a, ls, 1.0, 0.01)
+    np.testing.assert_allclose(mean, m_o, rtol=1e-6, atol=1e-9)
+    assert np.max(np.abs(std - s_o)) <= 1e-8
+    np.testing.assert_allclose(g.predict(Xq[:5]), m_o[:5], rtol=1e-6, atol=1e-9)

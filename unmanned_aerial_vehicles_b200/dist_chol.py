@@ -319,6 +319,7 @@ class DistGP:
     def factor(self, inv_ls, c, noise):
         o, NB, nb = self.ops, self.NB, self.nb
         side = o.side if self.lookahead else contextlib.nullcontext
+        self.theta = (tuple(float(v) for v in inv_ls), float(c), float(noise))
         self.assemble(inv_ls, c, noise)
         self._panel_factor(0, 0)
         with side():
@@ -403,3 +404,74 @@ class DistGP:
 
     def alpha_host(self):
         return self.ops.to_host(self.alpha_d)[: self.N]
+
+    # -- predict from the distributed factor ----------------------------------------------------------
+    def predict(self, Xq, return_std=False, chunk_rows=256):
+        """mean (M, T) [, std (M, T)] for query rows Xq (the SAME rows on every rank: the work is shared by tiles,
+        not by query rows), sklearn _gpr.py:446-500 without target normalisation.
+
+        Queries are a row tile of the factorisation: with Q = k(Xq, X) (m x N), the variance needs W = Q L^-T, block
+        column k of which is  W_k = (Q_k - sum_{j<k} W_j L_kj^T) L_kk^-T  -- the panel formula of `_panel_factor`, so
+        every product is one NT GEMM on the DMMA kernel.  Per block k: the owner of the diagonal tile forms Q_k in place
+        from the replicated X (never communicated), adds Q_k alpha_k to the mean, forms W_k and broadcasts it; the ranks
+        of process column k % Pc add W_k L_ik^T to their running sums for all owned rows i > k in ONE GEMM over the
+        stacked column; one all-reduce per block brings the sums of block k together.  sum_k rowsum(W_k^2) is taken
+        as the diagonal of sum_k W_k W_k^T (m x m, one more small GEMM per block).  m N^2 flops per chunk, shared by
+        the P ranks."""
+        assert self.factored and hasattr(self, "alpha_d"), "factor() and solve() first"
+        o, NB, nb, T, Pr, Pc = self.ops, self.NB, self.nb, self.T, self.Pr, self.Pc
+        inv_ls, c, noise = self.theta
+        Xq = np.ascontiguousarray(Xq, dtype=np.float64)
+        if Xq.ndim != 2 or Xq.shape[1] != self.D:
+            raise ValueError(f"X has {Xq.shape[1] if Xq.ndim == 2 else '?'} features, the training set {self.D}")
+        M = Xq.shape[0]
+        chunk_rows = max(128, (int(chunk_rows) // 128) * 128)
+        mean = np.empty((M, T))
+        std = np.empty((M, T)) if return_std else None
+        neg = 0
+        for s0 in range(0, M, chunk_rows):
+            m = min(chunk_rows, M - s0)
+            MP = ((m + 127) // 128) * 128
+            xq = o.from_host(Xq[s0:s0 + m])
+            Qk, acc = o.empty(MP, NB), o.zeros(MP, T)
+            if return_std:
+                Z = o.zeros(MP, max(self.nlr, 1) * NB)      # running sums for this rank's row tiles (local order)
+                W, t, G = o.empty(MP, NB), o.empty(MP, NB), o.zeros(MP, MP)
+            for k in range(nb):
+                blk = slice(k * NB, (k + 1) * NB)
+                own = self.owner(k) == self.rank
+                if return_std:
+                    if self.pr == k % Pr:
+                        lk = k // Pr
+                        o.copy(Z[:, lk * NB:(lk + 1) * NB], t)
+                    else:
+                        o.zero(t)
+                    o.allreduce_sum(t)
+                if own:
+                    nc = max(0, min(NB, self.N - k * NB))
+                    o.gram_block(xq, m, self.X_d[k * NB:], nc, self.D, inv_ls, c, Qk, MP, NB)
+                    o.gemv(Qk, self.alpha_d[blk], acc, 1.0, 1.0, transpose=False)
+                    if return_std:
+                        rhs = Qk - t
+                        o.gemm_nt(rhs, self.Ml[k], W, MP, NB, NB, 1.0, 0, b_tri=1)
+                if return_std:
+                    o.bcast(W, self.owner(k))
+                    o.gemm_nt(W, W, G, MP, MP, NB, 1.0, 1)
+                    if self.pc == k % Pc:
+                        off = NB if self.pr == k % Pr else 0
+                        rows = self.cols[k].shape[0] - off
+                        if rows > 0:
+                            l0 = self.lfirst(k + 1)
+                            o.gemm_nt(W, self.cols[k][off:], Z[:, l0 * NB:], MP, rows, NB, 1.0, 1)
+            o.allreduce_sum(acc)
+            mean[s0:s0 + m] = o.to_host(acc)[:m]
+            if return_std:
+                var = (c + noise) - np.diag(o.to_host(G))[:m]
+                neg += int((var < 0).sum())
+                std[s0:s0 + m] = np.sqrt(np.maximum(var, 0.0))[:, None]
+        if return_std:
+            if neg:
+                import warnings
+                warnings.warn("Predicted variances smaller than 0. Setting those variances to 0.")
+            return mean, std
+        return mean
