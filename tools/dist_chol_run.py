@@ -12,6 +12,7 @@ ap.add_argument("--size", dest="n", type=int, default=200000); ap.add_argument("
 ap.add_argument("--check", action="store_true")
 ap.add_argument("--grid", default="", help="PrxPc, e.g. 2x4 (default: most square)")
 ap.add_argument("--no-lookahead", action="store_true")
+ap.add_argument("--predict-rows", type=int, default=0, help="time DistGP.predict(return_std=True) on this many query rows")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
 torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
@@ -43,6 +44,26 @@ out = {"what": "dist_chol", "n": a.n, "nb": a.nb, "n_gpus": world, "grid": f"{g.
        "assemble_factor_s": t2 - t1, "solve_lml_s": t3 - t2, "lml": lml, "potrf_alg_tflops": (a.n ** 3 / 3) / (t2 - t1) / 1e12,
        "executed_gemm_tflops": float(fl[0]) / (t2 - t1) / 1e12, "max_mem_gib_per_gpu": float(mem[0]),
        "local_gib": g.local_bytes() / 2 ** 30}
+if a.predict_rows > 0:                                  # collective: every rank runs it on the same rows
+    Xq = X[np.random.default_rng(7).integers(0, a.n, a.predict_rows)] + 0.05
+    g.predict(Xq[:256], return_std=True)                # warm-up
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    tp = time.perf_counter()
+    pm, ps = g.predict(Xq, return_std=True)
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    tp = time.perf_counter() - tp
+    out.update({"predict_rows": a.predict_rows, "predict_mean_std_s": tp, "predict_pts_per_s": a.predict_rows / tp,
+                "predict_fp64_tflops_aggregate": a.predict_rows * float(g.NP) ** 2 / tp / 1e12})
+    if a.check and rank == 0:
+        from unmanned_aerial_vehicles_b200.engine import DeviceGP
+        e2 = DeviceGP(X, Y, jit)
+        assert e2.factor(1.0 / ls, 1.0, noise) == 0
+        m_e, s_e, _, _ = e2.predict(Xq, np.zeros(T), np.ones(T), True)
+        out["check_predict_mean_maxabs"] = float(np.max(np.abs(pm - m_e)))
+        out["check_predict_std_maxabs"] = float(np.max(np.abs(ps - s_e)))
+        del e2
 if a.check and rank == 0:
     from unmanned_aerial_vehicles_b200.engine import DeviceGP
     eng = DeviceGP(X, Y, jit)
