@@ -79,6 +79,36 @@ def cpu_eval_sample(n_sample, n_full, reps):
     return {"sample_eval_s": t_all, "sample_cubic_s": t_cubic, "scaled_eval_s": t_scaled}
 
 
+def stock_sklearn_sample(n_sample, n_full):
+    """The reference's own arithmetic, unrestated: scikit-learn's GaussianProcessRegressor.log_marginal_likelihood(theta,
+    eval_gradient=True) (_gpr.py:541-656; it materialises the (N, N, n_theta) gradient tensor, so it is run at a size
+    that fits: 10 x 8 N^2 bytes) -- one evaluation, scaled to n_full like the port's sample."""
+    import warnings
+
+    from scipy.linalg import cho_solve, cholesky
+    from sklearn.gaussian_process import GaussianProcessRegressor as SkGPR
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+
+    X, Y = make_data(n_sample)
+    k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * D, (0.1, 10.0)) + WhiteKernel(NOISE0, (1e-5, 10.0))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        g = SkGPR(kernel=k, alpha=JITTER, optimizer=None).fit(X, Y)
+        th = theta_sequence(0, 1)[0]
+        t0 = time.perf_counter()
+        g.log_marginal_likelihood(th, eval_gradient=True)
+        t_all = time.perf_counter() - t0
+    K = g.kernel_(X)
+    K[np.diag_indices_from(K)] += JITTER
+    t0 = time.perf_counter()
+    L = cholesky(K, lower=True, check_finite=False)
+    cho_solve((L, True), np.eye(n_sample), check_finite=False)
+    t_cubic = min(time.perf_counter() - t0, t_all)
+    r = n_full / n_sample
+    return {"n": n_sample, "eval_s": t_all, "cubic_s": t_cubic, "scaled_eval_s": t_cubic * r ** 3 + (t_all - t_cubic) * r ** 2,
+            "what": "sklearn GaussianProcessRegressor.log_marginal_likelihood(theta, eval_gradient=True), one evaluation"}
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -102,6 +132,9 @@ def reference_arm(args):
                   f"scaled to N={args.n}: cubic x r^3 + rest x r^2")
     value = 1.0 / eval_s
     cores = os.cpu_count()
+    stock = None
+    if not args.cpu_full and not args.no_stock_sklearn:
+        stock = stock_sklearn_sample(min(3000, args.n), args.n)     # reported beside the lean port, which is faster
     line = {
         "impl": "reference", "metric": metric_name(args.n), "value": value, "unit": "evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": eval_s * 1e3,
@@ -112,6 +145,8 @@ def reference_arm(args):
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if stock is not None:
+        line["cpu_baseline"]["stock_sklearn"] = stock
     print(json.dumps(line), flush=True)
 
 
@@ -341,6 +376,7 @@ def main():
     ap.add_argument("--predict-rows", type=int, default=81920)
     ap.add_argument("--full-fit", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stock-sklearn", action="store_true")
     args = ap.parse_args()
     global T
     T = args.targets

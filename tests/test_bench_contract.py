@@ -20,6 +20,8 @@ def test_reference_arm_prints_contract_line():
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "N=2000 D=9 T=3" in line["config"]["workload"]
+    stock = line["cpu_baseline"]["stock_sklearn"]          # the reference's own arithmetic beside the lean port
+    assert stock["n"] == 2000 and stock["eval_s"] > 0 and stock["scaled_eval_s"] >= stock["eval_s"] * 0.999
 
 
 def test_non_zero_ranks_of_the_reference_arm_do_nothing():
