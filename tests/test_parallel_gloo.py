@@ -151,3 +151,58 @@ def test_trainer_components_sharded_over_two_ranks_equal_the_serial_loop(tmp_pat
             np.testing.assert_allclose(out[1][n][:2], serial[0][n][:2], rtol=1e-12)
         np.testing.assert_allclose(out[2], serial[1], rtol=1e-10, atol=1e-13)
         np.testing.assert_allclose(out[3], serial[2], rtol=1e-10, atol=1e-13)
+
+
+def _run_config4_shape():
+    """three single-output ARD models x 4 optimiser runs each through parallel.fit_outputs_sharded_restarts (engine
+    double: no GPU here); returns theta*, LML and a prediction per model"""
+    import warnings
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+    from test_estimator_host_logic import OracleEngine
+    from unmanned_aerial_vehicles_b200 import gpr as gpr_mod, parallel
+    real, gpr_mod.DeviceGP = gpr_mod.DeviceGP, OracleEngine
+    try:
+        X, Y = _trainer_case()
+        k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 4, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0))
+        make = lambda t: gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, n_restarts_optimizer=3, random_state=10 + t)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            models = parallel.fit_outputs_sharded_restarts(make, X, Y)
+            assert all(m._engine is None for m in models)                      # device buffers released per output
+            out = [(m.kernel_.theta.tolist(), float(m.log_marginal_likelihood_value_),
+                    np.asarray(m.predict(X[:3] + 0.01)).tolist()) for m in models]
+    finally:
+        gpr_mod.DeviceGP = real
+    return out
+
+
+def _config4_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    q.put((rank, _run_config4_shape()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_outputs_in_turn_with_restarts_sharded_equal_the_serial_fits():
+    """BASELINE config 4's sharding (outputs one after the other, each model's optimiser runs over all ranks): every
+    rank ends with the serial fits' theta*, LML and predictions."""
+    sys.path.insert(0, ROOT)
+    serial = _run_config4_shape()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_config4_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    outs = sorted(q.get(timeout=300) for _ in range(2))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for _, got in outs:
+        assert len(got) == 3
+        for (th, lml, pred), (th0, lml0, pred0) in zip(got, serial):
+            np.testing.assert_allclose(th, th0, rtol=0, atol=1e-12)
+            assert lml == pytest.approx(lml0, rel=1e-12)
+            np.testing.assert_allclose(pred, pred0, rtol=1e-10, atol=1e-13)

@@ -61,6 +61,23 @@ def fit_sharded_outputs(make_estimator, X, Y, group=None):
     return run_sharded(lambda t: make_estimator(t).fit(X, Y[:, t]), cols, group)
 
 
+def fit_outputs_sharded_restarts(make_estimator, X, Y, group=None, release_device=True):
+    """BASELINE config 4 (3 outputs x 32 restarts over 8 GPUs at N=50k): one single-output model per column of Y,
+    fitted one after the other, each with its optimiser runs sharded over ALL ranks (32 runs / 8 ranks = 4 each, so
+    12 runs per GPU in total -- sharding the three outputs instead would leave five GPUs idle).  Every rank ends
+    with every fitted estimator.  ``release_device`` drops each model's device buffers (three NP x NP matrices:
+    60 GB at N=50k) once it is fitted, so the next output's factorisation fits beside it; predict re-creates them
+    lazily from ``kernel_`` (one Gram + factorisation)."""
+    models = []
+    for t in range(Y.shape[1]):
+        est = fit_sharded_restarts(make_estimator(t), X, Y[:, t], group)
+        if release_device:
+            est._engine = None
+            est._low = None
+        models.append(est)
+    return models
+
+
 def row_block(n_rows: int, rank: int, world: int):
     """contiguous [lo, hi) block of query rows owned by `rank`"""
     base, rem = divmod(n_rows, world)
