@@ -426,3 +426,40 @@ def test_enhanced_mpc_residuals_follow_the_reference_loop(tmp_path):
     _, _, pC2, *_ = _schema_pickles(tmp_path, drop={"vy_residual"})
     g2 = callers.EnhancedMPCResiduals(pC2)
     assert not g2.gp_available and not np.any(g2.predict_gp_residuals(state, control))
+
+
+def test_fit_from_theta_rebuilds_the_fitted_estimator_without_the_optimiser():
+    """parallel.py ships only (theta*, lml*) between ranks: the rebuilt estimator must equal the fitted one, with the
+    factorisation deferred until alpha_ / L_ / predict is touched (no N x N matrix crosses ranks)."""
+    X, Y = _data(60, 3, 2, seed=5)
+    k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 3, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        g = gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, n_restarts_optimizer=1, normalize_y=True,
+                                             random_state=0).fit(X, Y)
+    assert g.n_lml_evals_ > 2                                  # objective evaluations of the optimiser runs are counted
+    r = gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, n_restarts_optimizer=1, normalize_y=True,
+                                         random_state=0).fit_from_theta(X, Y, g.kernel_.theta,
+                                                                        g.log_marginal_likelihood_value_)
+    assert r._engine is None and "_alpha_cache" not in r.__dict__ and r.n_lml_evals_ == 0     # nothing computed yet
+    assert str(r.kernel_) == str(g.kernel_) and r.log_marginal_likelihood() == g.log_marginal_likelihood()
+    np.testing.assert_array_equal(r.y_train_, g.y_train_)
+    np.testing.assert_array_equal(r.alpha_, g.alpha_)         # lazy: first access factors
+    np.testing.assert_array_equal(r.L_, g.L_)
+    for a, b in zip(r.predict(X[:5] + 0.1, return_std=True), g.predict(X[:5] + 0.1, return_std=True)):
+        np.testing.assert_array_equal(a, b)
+    r2 = gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, normalize_y=True).fit_from_theta(X, Y, g.kernel_.theta)
+    assert r2.log_marginal_likelihood() == pytest.approx(g.log_marginal_likelihood(), rel=1e-9)   # lml=None evaluates it
+    back = pickle.loads(pickle.dumps(r))
+    np.testing.assert_array_equal(back.alpha_, g.alpha_)
+
+
+@pytest.mark.parametrize("n_targets", [None, 3])
+def test_prior_covariance_matches_sklearn(n_targets):
+    """_gpr.py:417-443: predict before fit answers from the prior, including return_cov"""
+    k = CK(2.0) * RBF([0.5, 1.5]) + WhiteKernel(0.1)
+    Xq = np.random.default_rng(2).standard_normal((7, 2))
+    ms, cs = SkGPR(kernel=k, n_targets=n_targets).predict(Xq, return_cov=True)
+    mg, cg = gpr_mod.GaussianProcessRegressor(kernel=k, n_targets=n_targets).predict(Xq, return_cov=True)
+    assert mg.shape == ms.shape and cg.shape == cs.shape
+    np.testing.assert_allclose(cg, cs, rtol=0, atol=1e-15)

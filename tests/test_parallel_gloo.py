@@ -51,7 +51,25 @@ def _worker(rank, world, port, q):
         r = scipy.optimize.minimize(f, t0, method="L-BFGS-B", jac=True, bounds=[(-3, 3), (-8, 1)])
         return r.x, r.fun
     starts = [np.array([0.0, -2.0])] + [np.random.RandomState(1).uniform([-3, -8], [3, 1]) for _ in range(4)]
-    res = parallel.run_sharded(run_one, starts)
+    res = parallel.run_sharded(run_one, starts)                      # dynamic queue: first come, first served
+    n_dyn = len(calls)
+    assert parallel.last_stats["schedule"] == "dynamic" and len(parallel.last_stats["items"]) == n_dyn
+    res_static = parallel.run_sharded(run_one, starts, schedule="static")
+    assert len(calls) - n_dyn == (3 if rank == 0 else 2)             # 5 runs round-robin over 2 ranks
+    assert all(np.array_equal(a[0], b[0]) and a[1] == b[1] for a, b in zip(res, res_static))
+    stats = parallel.gather_stats()
+    assert sorted(i for st in stats for i in st["items"]) == [0, 1, 2, 3, 4]
+
+    def boom(v):                                                     # a failure on ONE rank surfaces on EVERY rank
+        if v == 3:
+            raise np.linalg.LinAlgError("not positive definite")
+        return v
+    for sched in ("static", "dynamic"):
+        try:
+            parallel.run_sharded(boom, [0, 1, 2, 3], schedule=sched)
+            raise AssertionError("expected ShardedWorkError")
+        except parallel.ShardedWorkError as e:
+            assert "LinAlgError" in str(e) and "work item 3" in str(e)
     lo, hi = parallel.row_block(11, rank, world)
 
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -62,10 +80,19 @@ def _worker(rank, world, port, q):
     assert fk.seen == hi - lo and np.array_equal(m, Xq @ np.array([1.0, -2.0])) and np.array_equal(sd, np.abs(m) + 1.0)
     own = parallel.predict_sharded(Fake(), Xq, gather=False)
     assert np.array_equal(own, (Xq @ np.array([1.0, -2.0]))[lo:hi])
+
+    class Fake2(Fake):                                               # multi-target outputs stay 2-D through the gather
+        def predict(self, Xq, return_std=False):
+            m = np.stack([Xq[:, 0], Xq[:, 1], Xq.sum(1)], 1)
+            return (m, m * m) if return_std else m
+    m2, s2 = parallel.predict_sharded(Fake2(), Xq, return_std=True)
+    assert m2.shape == (11, 3) and np.array_equal(m2[:, 2], Xq.sum(1)) and np.array_equal(s2, m2 * m2)
+    one = parallel.predict_sharded(Fake2(), Xq[:1])                  # rank 1's block is empty
+    assert one.shape == (1, 3) and np.array_equal(one[0], [Xq[0, 0], Xq[0, 1], Xq[0].sum()])
     Y3 = np.stack([y, 2 * y, y + 1.0], 1)
     models = parallel.fit_sharded_outputs(lambda t: Fake(t), X, Y3)
     assert [mm.t for mm in models] == [0, 1, 2] and np.allclose([mm.mu for mm in models], Y3.mean(0))
-    q.put((rank, len(calls), [(list(map(float, a)), float(b)) for a, b in res], (lo, hi)))
+    q.put((rank, n_dyn, [(list(map(float, a)), float(b)) for a, b in res], (lo, hi)))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -80,7 +107,7 @@ def test_sharded_restarts_match_serial():
     [p.join(60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
     (r0, n0, res0, blk0), (r1, n1, res1, blk1) = outs
-    assert n0 == 3 and n1 == 2            # 5 runs round-robin over 2 ranks
+    assert n0 + n1 == 5                   # 5 runs claimed from the shared counter, each by exactly one rank
     assert res0 == res1 and len(res0) == 5  # every rank holds every result, in start order
     assert blk0 == (0, 6) and blk1 == (6, 11)
     best = int(np.argmin([f for _, f in res0]))

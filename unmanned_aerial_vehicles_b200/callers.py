@@ -443,15 +443,28 @@ class GPTrainer:
         X_train, X_test, y_train, y_test = train_test_split(X, y, test_size=test_size, random_state=42)
         todo = [(i, name) for i, name in enumerate(OUTPUT_NAMES[: y.shape[1]]) if np.std(y_train[:, i]) >= 1e-6]
 
+        kept = {}
+
+        def scaled(i):
+            sX, sY = StandardScaler(), StandardScaler()
+            return sX, sY, sX.fit_transform(X_train), sY.fit_transform(y_train[:, i].reshape(-1, 1)).flatten()
+
         def fit_one(item):
             i, name = item
-            sX, sY = StandardScaler(), StandardScaler()
-            Xs = sX.fit_transform(X_train)
-            ys = sY.fit_transform(y_train[:, i].reshape(-1, 1)).flatten()
-            return sX, sY, self._make_estimator(X.shape[1], i).fit(Xs, ys)
+            sX, sY, Xs, ys = scaled(i)
+            kept[name] = (sX, sY, self._make_estimator(X.shape[1], i).fit(Xs, ys))
+            gp = kept[name][2]
+            return np.array(gp.kernel_.theta), float(gp.log_marginal_likelihood_value_)
 
-        fitted = run_sharded(fit_one, todo, self.group)     # pickled across ranks as host NumPy, refactored lazily
-        for (i, name), (sX, sY, gp) in zip(todo, fitted):
+        # only (theta*, lml*) crosses ranks; the other ranks rebuild each model from them (scalers are a function of
+        # the split every rank holds) and factor lazily at the first predict -- no N x N matrix is pickled
+        fitted = run_sharded(fit_one, todo, self.group)
+        for (i, name), (theta, lml) in zip(todo, fitted):
+            if name in kept:
+                sX, sY, gp = kept[name]
+            else:
+                sX, sY, Xs, ys = scaled(i)
+                gp = self._make_estimator(X.shape[1], i).fit_from_theta(Xs, ys, theta, lml)
             self.gp_models[name], self.scalers_X[name], self.scalers_y[name] = gp, sX, sY
         results = {}
         if todo:

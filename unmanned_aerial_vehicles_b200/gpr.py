@@ -61,7 +61,9 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
             self._engine = eng
         return eng
 
-    def fit(self, X, y):
+    def _prepare_fit(self, X, y):
+        """Everything of fit() before the optimiser (_gpr.py:249-300): kernel clone, validation, target
+        normalisation, training-set copies.  Returns the lowered kernel template."""
         self.kernel_ = C(1.0, constant_value_bounds="fixed") * RBF(1.0, length_scale_bounds="fixed") \
             if self.kernel is None else clone(self.kernel)
         self._rng = check_random_state(self.random_state)
@@ -86,10 +88,32 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         self.y_train_ = np.copy(y) if self.copy_X_train else y
         self._engine = None
         self._low = None
-        template = lower(self.kernel_, X.shape[1])  # raises early for unsupported kernels
+        self.__dict__.pop("_L_cache", None)
+        self.__dict__.pop("_alpha_cache", None)
+        self.n_lml_evals_ = 0
+        return lower(self.kernel_, X.shape[1])  # raises early for unsupported kernels
+
+    def fit_from_theta(self, X, y, theta, lml=None, finalize=False):
+        """The fitted estimator ``fit(X, y)`` would return if its optimiser ended at ``theta`` -- without running
+        the optimiser.  parallel.py uses it to rebuild, on the other ranks, a model one rank has fitted: only
+        (theta*, lml*) travel, never an N x N factor.  The factorisation (`L_`, `alpha_`) is deferred to first use
+        unless ``finalize``; ``lml=None`` evaluates it."""
+        self._prepare_fit(X, y)
+        self.kernel_.theta = np.asarray(theta, dtype=np.float64)
+        self.kernel_._check_bounds_params()
+        self.log_marginal_likelihood_value_ = float(lml) if lml is not None else \
+            self.log_marginal_likelihood(self.kernel_.theta, clone_kernel=False)
+        if finalize:
+            self._finalize_factor()
+        return self
+
+    def fit(self, X, y):
+        template = self._prepare_fit(X, y)
+        X = self.X_train_
 
         if self.optimizer is not None and self.kernel_.n_dims > 0:
             def obj_func(theta, eval_gradient=True):
+                self.n_lml_evals_ += 1
                 # _gpr.py:302-310 with clone_kernel=False, minus the per-evaluation walk over sklearn's kernel
                 # objects: theta goes straight to the flat parameter set (kernel_.theta is set once, at the end)
                 low = template.with_theta(theta)
@@ -137,8 +161,22 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         self._low = low
         self._yscale_b = (np.broadcast_to(self._y_train_mean, (eng.T,)), np.broadcast_to(self._y_train_std, (eng.T,)))
         a = eng.alpha_host()
-        self.alpha_ = a if self.y_train_.ndim == 2 else a[:, 0]
+        self.__dict__["_alpha_cache"] = a if self.y_train_.ndim == 2 else a[:, 0]
         self.__dict__.pop("_L_cache", None)
+
+    @property
+    def alpha_(self):
+        """K^-1 y (_gpr.py:363-367); computed with the factorisation on first access when the estimator was
+        rebuilt from hyper-parameters (fit_from_theta, unpickling)."""
+        if "_alpha_cache" not in self.__dict__:
+            if not hasattr(self, "X_train_"):
+                raise AttributeError("alpha_")
+            self._finalize_factor()
+        return self.__dict__["_alpha_cache"]
+
+    @alpha_.setter
+    def alpha_(self, value):
+        self.__dict__["_alpha_cache"] = value
 
     @property
     def L_(self):
@@ -172,7 +210,12 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
             y_mean = np.zeros(shape=(X.shape[0], n_targets)).squeeze()
             low = lower(kernel, X.shape[1])
             if return_cov:
-                raise NotImplementedError("prior covariance is not on the B200 path; fit first")
+                # _gpr.py:432-436: the prior covariance is the kernel itself on the query rows -- no training set,
+                # no factor, nothing for the device to do; evaluated by the kernel object on the host
+                y_cov = kernel(X)
+                if n_targets > 1:
+                    y_cov = np.repeat(np.expand_dims(y_cov, -1), repeats=n_targets, axis=-1)
+                return y_mean, y_cov
             if return_std:
                 y_var = np.full(X.shape[0], low.c + low.noise)
                 if n_targets > 1:
@@ -256,15 +299,20 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
         state.pop("_low", None)
         state.pop("_yscale_b", None)
         L = state.pop("_L_cache", None)
+        a = state.pop("_alpha_cache", None)
         if fitted:
             state["L_"] = L if L is not None else self.L_
+            state["alpha_"] = a if a is not None else self.alpha_
         return state
 
     def __setstate__(self, state):
         L = state.pop("L_", None)
+        a = state.pop("alpha_", None)
         self.__dict__.update(state)
         if L is not None:
             self.__dict__["_L_cache"] = L
+        if a is not None:
+            self.__dict__["_alpha_cache"] = a
         self._engine = None
         self._low = None
 
