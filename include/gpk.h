@@ -36,7 +36,9 @@ int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, 
              double* K_d, int NP, int lower_only, void* stream);
 
 /* scipy.linalg.cholesky (dpotrf) at _gpr.py:352,591 fused with the triangular inverse.
- * A_d in: lower triangle of K, out: lower factor L.  Mlow_d = L^-1 (lower), Mup_d = L^-T (upper). */
+ * A_d in: lower triangle of K, out: lower factor L; the 128-blocks strictly above the diagonal of A_d are used as
+ * scratch.  Mlow_d = L^-1 (lower), Mup_d = L^-T (upper).  One enqueue at a time per device (internal mutex: the
+ * recursion's side streams are per device); safe to call from several host threads. */
 int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream);
 
 /* cho_solve((L, True), y) at _gpr.py:363,601 via the explicit inverse: u = L^-1 y, alpha = L^-T u.
@@ -56,7 +58,9 @@ int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double
 
 /* one whole log_marginal_likelihood(theta, eval_gradient) evaluation (_gpr.py:541-656):
  * gram -> potrf_inv -> potrs -> [lauum -> gradient] -> finalize.  A_d, Mlow_d, Mup_d are NP x NP scratch
- * (A_d ends as K^-1 lower tiles when with_grad, else as L).  y_d (NP x T, zero padded). */
+ * (A_d ends as K^-1 lower tiles when with_grad, else with L's diagonal 128-blocks only: an objective evaluation
+ * needs log det alone of L, so the off-diagonal panels stay where their GEMM left them, in Mlow_d, until the inverse
+ * overwrites them; gpk_potrf_inv is the call that returns L).  y_d (NP x T, zero padded). */
 int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
                  const double* y_d, int T, double* A_d, double* Mlow_d, double* Mup_d, double* u_d, double* alpha_d,
                  int NP, int with_grad, double* ws_d, double* out_d, int* info_d, void* stream);
@@ -69,6 +73,15 @@ int gpk_cross_gram(const double* Xq_d, int Mq, const double* X_d, int N, int D, 
 int gpk_predict_mean(const double* Ks_d, int Mq, int N, int NP, const double* alpha_d, int T, const double* y_mean_d,
                      const double* y_std_d, double* mean_d, void* stream);
 
+/* _gpr.py:446-454 with return_std=False (evaluate_gp_offline.py:198, gp_enhanced_mpc.py:165,175), fused: the
+ * cross-Gram row is consumed as it is produced, no Ks in HBM.  Xq_d (Mq x D), MP = Mq rounded up to 64 (or more);
+ * partial_d: scratch of gpk_predict_mean_workspace_doubles(MP, N, D, T) doubles (that figure also covers the staged
+ * query rows and the result when gpk_predict carves them from one block); mean_d (Mq x T). */
+size_t gpk_predict_mean_workspace_doubles(int MP, int N, int D, int T);
+int gpk_predict_mean_fused(const double* Xq_d, int Mq, int MP, const double* X_d, int N, int D, const double* inv_ls_h,
+                           double c, const double* alpha_d, int T, const double* y_mean_d, const double* y_std_d,
+                           double* partial_d, double* mean_d, void* stream);
+
 /* _gpr.py:460-500: V = Ks L^-T, var = prior - rowsum(V^2) clamped at 0, std = sqrt(var * y_std^2).
  * rowsq_d: scratch MP x (NP/64).  *neg_d is incremented per clamped row (the caller warns). */
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,
@@ -78,7 +91,8 @@ int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, in
  * tick): Xq_h (Mq x D) host -> mean_h (Mq x T) host [, std_h (Mq x T) host, *neg_h = rows whose variance was
  * clamped at 0].  H2D, cross-Gram, mean, L^-1 contraction, std, D2H and one stream sync happen inside.
  * X_d, alpha_d, Mlow_d, y_mean_d, y_std_d are the device-resident model; ws_d is device scratch of at least
- * gpk_predict_workspace_doubles(MP = Mq rounded up to 128, NP, D, T) doubles.  std_h may be NULL (mean only). */
+ * gpk_predict_workspace_doubles(MP = Mq rounded up to 128, NP, D, T) doubles.  std_h may be NULL: mean only, which
+ * takes the fused kernel above and needs only gpk_predict_mean_workspace_doubles(MP, N, D, T) doubles of scratch. */
 size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T);
 int gpk_predict(const double* Xq_h, int Mq, int D, const double* X_d, int N, const double* inv_ls_h, double c,
                 double noise, const double* alpha_d, int T, const double* Mlow_d, int NP, const double* y_mean_d,
@@ -125,35 +139,6 @@ int gpk_trimv(const double* M_d, int NP, const double* v_d, double* out_d, int T
 int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pad_value, void* stream);
 /* *sum_d += sum_i log A[i,i], i < n */
 int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
-
-/* EXPERIMENTAL (off unless GPK_I8 is set, see below): FP64-accurate C = alpha * A * B^T on the tcgen05
- * INT8 pipe.  Operands are pre-split into S int8 slice planes with one power-of-two scale per row:
- *   a[i,k] = mu[i] * sum_s planes[s][i][k] * 2^-(6+7s),   |planes| <= 64,   planes laid out [S][rowsP][KP], K contiguous.
- * gpk_i8_slice: src_d (rows x K, leading dimension ld; tri = 0 full, 1 lower, 2 upper: only that triangle is read)
- *   -> planes_d (S * rowsP * KP bytes, zero padded), mu_d (rowsP).  rowsP multiple of 64 (128 for a left operand),
- *   KP multiple of 64.
- * gpk_i8_gemm_nt: A planes (M x KP), B planes (N x KP), S(S+1)/2 exact slice products in int32 tensor-memory
- *   accumulators, combined in FP64.  Same meaning of accumulate / a_tri / b_tri / lower_only as gpk_gemm_nt.
- *   rowsq_d != NULL: nothing is stored to C; rowsq_d (M x N/64) receives per-tile row sums of squares (predict's
- *   variance contraction).  M multiple of 128, N and KP multiples of 64, S * KP < 2^19. */
-int gpk_i8_slice(const double* src_d, int ld, int rows, int K, int tri, int S, signed char* planes_d, int rowsP, int KP,
-                 double* mu_d, void* stream);
-int gpk_i8_gemm_nt(const signed char* Aq_d, const double* mu_a_d, int M, const signed char* Bq_d, const double* mu_b_d,
-                   int N, int KP, int S, double* C_d, int ldc, double alpha, int accumulate, int a_tri, int b_tri,
-                   int lower_only, double* rowsq_d, void* stream);
-/* EXPERIMENTAL opt-in use of the two calls above on the estimator's path (engine.py does this only when the
- * environment sets GPK_I8; default: never).  gpk_i8_configure registers caller-owned device scratch of at least
- * gpk_i8_workspace_bytes(NP, MPmax, S) bytes for the current device; mode bit 1: gpk_lml_eval forms K^-1 = L^-T L^-1
- * from int8 planes of L^-T; bit 2: gpk_predict / gpk_predict_std form the variance contraction Ks L^-T from planes of
- * L^-1 that gpk_i8_prepare_predict(Mlow_d) sliced after the final factorisation (any later gpk_potrf_inv /
- * gpk_lml_eval drops them); bit 4: gpk_lml_eval (never gpk_potrf_inv) forms the inverse blocks that no later panel
- * of the factorisation reads -- those of the right-most path of its recursion -- from int8 planes as well.  Shapes the int8 kernel cannot take (NP or the padded query rows not a multiple of 128,
- * more query rows than MPmax) silently use the FP64 DMMA kernel.  ws_d = NULL or mode = 0 switches it off.
- * gpk_i8_workspace_bytes returns 0 for an unsupported shape; gpk_i8_mode returns the active mode bits. */
-size_t gpk_i8_workspace_bytes(int NP, int MPmax, int S);
-int gpk_i8_configure(void* ws_d, size_t bytes, int NP, int MPmax, int S, int mode);
-int gpk_i8_prepare_predict(const double* Mlow_d, int NP, void* stream);
-int gpk_i8_mode(void);
 
 /* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
  * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */

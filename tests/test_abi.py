@@ -30,7 +30,7 @@ def test_pure_host_entry_points():
     assert lib.gpk_pad(1) == 128 and lib.gpk_pad(128) == 128 and lib.gpk_pad(129) == 256
     assert lib.gpk_pad(20000) == 20096
     assert lib.gpk_lml_out_len(9, 3) == 2 + 3 + 1 + 9 + 1
-    assert lib.gpk_grad_workspace_doubles(1000, 10) == (1024 // 64) ** 2 * 14 + 1024
+    assert lib.gpk_grad_workspace_doubles(1000, 10) == (1024 // 64) ** 2 * 12 + 1024   # D=9,10 -> padded to 10
 
 
 def test_no_cpu_fallback_without_cuda():
@@ -49,20 +49,16 @@ def test_no_cpu_fallback_without_cuda():
         g.fit(np.random.rand(10, 2), np.random.rand(10))
 
 
-def test_int8_opt_in_registration_is_pure_host_and_off_by_default():
+def test_workspace_queries_are_pure_host():
     lib = _lib.load()
-    assert lib.gpk_i8_mode() == 0                                             # nothing enabled unless asked
-    al = lambda b: (b + 255) & ~255
-    NP, MP, S = 20096, 16384, 7
-    want = 2 * (al(S * NP * NP) + al(8 * NP)) + al(S * MP * NP) + al(8 * MP)
-    assert lib.gpk_i8_workspace_bytes(NP, MP, S) == want
-    assert lib.gpk_i8_workspace_bytes(NP + 64, MP, S) == 0                    # NP must be a multiple of 128
-    assert lib.gpk_i8_workspace_bytes(NP, MP, 9) == 0                         # at most 8 slices (512 TMEM columns)
-    fake = ctypes.c_void_p(0x1000)                                            # never dereferenced by configure
-    assert lib.gpk_i8_configure(fake, want - 1, NP, MP, S, 3) == -2 and lib.gpk_i8_mode() == 0
-    assert lib.gpk_i8_configure(fake, want, NP, MP, 8, 3) != 0 and lib.gpk_i8_mode() == 0
-    assert lib.gpk_i8_configure(fake, want, NP, MP, S, 3) == 0 and lib.gpk_i8_mode() == 3
-    assert lib.gpk_i8_configure(None, 0, 0, 0, 0, 0) == 0 and lib.gpk_i8_mode() == 0
+    NP, MP, D, T = 20096, 8192, 9, 3
+    full = lib.gpk_predict_workspace_doubles(MP, NP, D, T)
+    mean_only = lib.gpk_predict_mean_workspace_doubles(MP, 20000, D, T)
+    assert full >= MP * NP + MP * D + 2 * MP * T and full >= mean_only      # one scratch serves both branches
+    assert mean_only >= MP * D + 2 * MP * T and mean_only < full // 100      # no M x N term in the fused branch
+    # few query rows: the training rows are split over enough CTAs to fill the GPU, one partial sum per split
+    assert lib.gpk_predict_mean_workspace_doubles(128, 20000, D, T) >= 128 * D + 128 * T * (1 + 148)
+    assert lib.gpk_predict_mean_workspace_doubles(100, 20000, D, T) == 0     # MP must be a multiple of 64
 
 
 def test_stacked_predict_argument_block_is_marshalled_field_by_field():

@@ -181,65 +181,6 @@ def test_sklearn_estimator_checks_pass():
     assert sum(r["status"] == "passed" for r in results) >= 50
 
 
-def test_int8_scratch_ownership_protocol_between_engines_on_one_device():
-    """engine.DeviceGP._i8_bind with a recording stand-in for libgpk: libgpk keeps one registered int8 scratch per
-    device, so an opt-in engine re-registers when another engine's scratch is in place, re-slices L^-1 exactly when
-    its planes were lost, and an engine built without the opt-in switches the registration off for its own calls."""
-    import types
-
-    from unmanned_aerial_vehicles_b200 import engine as eng_mod
-
-    calls = []
-
-    class Lib:
-        def gpk_i8_configure(self, ws, nbytes, NP, MPmax, S, mode):
-            calls.append(("configure", None if ws is None else ws.value, mode))
-            return 0
-
-        def gpk_i8_prepare_predict(self, mlow, NP, st):
-            calls.append(("prepare", mlow.value))
-            return 0
-
-    class Buf:
-        def __init__(self, ptr):
-            self.ptr = ptr
-
-        def data_ptr(self):
-            return self.ptr
-
-    def make(ptr, mode):
-        e = object.__new__(eng_mod.DeviceGP)
-        e.lib, e.device, e.NP = Lib(), types.SimpleNamespace(index=0), 1024
-        e.i8_mode, e._i8_planes_ok = mode, False
-        e._i8_ws, e._i8_cfg, e.Mlow_d = Buf(ptr), (4096, 1024, 1024, 7, mode), Buf(ptr + 1)
-        e._stream = lambda: None
-        return e
-
-    eng_mod._I8_OWNER.clear()
-    a, b, plain = make(0x1000, 3), make(0x2000, 3), make(0x3000, 0)
-    plain._i8_bind(need_planes=True)
-    assert calls == []                                           # nothing registered yet: a default engine does nothing
-    a._i8_bind()
-    a._i8_bind(need_planes=True)
-    a._i8_bind(need_planes=True)
-    assert calls == [("configure", 0x1000, 3), ("prepare", 0x1001)]      # registered once, sliced once
-    b._i8_bind(need_planes=True)
-    assert calls[2:] == [("configure", 0x2000, 3), ("prepare", 0x2001)]
-    a._i8_bind(need_planes=True)                                 # a lost both its registration and its planes
-    assert calls[4:] == [("configure", 0x1000, 3), ("prepare", 0x1001)]
-    plain._i8_bind(need_planes=True)                             # default engine: switches the opt-in off for its calls
-    assert calls[6:] == [("configure", None, 0)]
-    a._i8_planes_ok = False                                      # what lml()/factor() do before overwriting L^-1
-    a._i8_bind()
-    assert calls[7:] == [("configure", 0x1000, 3)]
-    a._i8_bind(need_planes=True)
-    assert calls[8:] == [("prepare", 0x1001)]
-    only_lauum = make(0x4000, 1)
-    only_lauum._i8_bind(need_planes=True)                        # mode without the predict bit never slices L^-1
-    assert calls[9:] == [("configure", 0x4000, 1)]
-    eng_mod._I8_OWNER.clear()
-
-
 @pytest.mark.parametrize("return_std", [False, True])
 def test_predict_stacked_equals_the_per_model_loop(monkeypatch, return_std):
     """gpr.predict_stacked (one device call for the per-output members of schema B / C pickles): same values and

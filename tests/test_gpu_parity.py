@@ -289,3 +289,35 @@ def test_small_batch_variance_path_matches_gemm_path(n):
     m_o, s_o = orc.predict(Xq, X, L, a, ls, 1.0, 0.02)
     np.testing.assert_allclose(m_big, m_o, rtol=1e-6, atol=1e-9)
     assert np.max(np.abs(s_big - s_o)) <= 1e-8
+
+
+@pytest.mark.parametrize("n,d,t,m", [(333, 3, 1, 1), (1000, 10, 6, 25), (700, 9, 3, 300), (2100, 9, 3, 5000),
+                                     (500, 14, 10, 130), (900, 20, 2, 77), (400, 8, 4, 64)])
+def test_mean_only_predict_fused_kernel(n, d, t, m):
+    """return_std=False (evaluate_gp_offline.py:198, gp_enhanced_mpc.py:165,175) takes the fused kernel: no cross-Gram
+    in HBM.  Against the oracle's K* alpha (_gpr.py:446-454) at 1e-6 relative (north star) -- in fact ~1e-13 -- and
+    against the two-pass route (cross-Gram, then K* alpha) the return_std=True call takes, over every feature padding
+    (4/8/10/12/16/32), both target widths (4, 8, two passes beyond 8), one query tile or many, splits of the
+    training rows or one."""
+    X, Y = _data(n, d, t, seed=11)
+    if t == 1:
+        Y = Y[:, 0]
+    ls = np.linspace(0.7, 2.2, d)
+    k = CK(1.7) * RBF(ls, (0.1, 10)) + WhiteKernel(0.02, (1e-5, 10))
+    g = GaussianProcessRegressor(kernel=k, alpha=1e-6, optimizer=None, normalize_y=True).fit(X, Y)
+    rng = np.random.default_rng(5)
+    Xq = np.vstack([X[: m // 2] + 1e-3, rng.standard_normal((m - m // 2, d)) * 1.5])
+    got = g.predict(Xq)
+    two_pass, _ = g.predict(Xq, return_std=True)
+    assert got.shape == two_pass.shape
+    L, a = orc.factor(X, g.y_train_, ls, 1.7, 0.02, 1e-6)
+    want, _ = orc.predict(Xq, X, L, a, ls, 1.7, 0.02, g._y_train_mean, g._y_train_std, return_std=False)
+    want = want[:, 0] if got.ndim == 1 else want
+    scale = np.abs(want).max()
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-9 * scale)
+    np.testing.assert_allclose(got, two_pass, rtol=0, atol=1e-11 * scale)
+    # many chunks == one, up to the summation order (the number of training-row splits follows the chunk height)
+    chunked = g._engine.predict(Xq, g._yscale_b[0], g._yscale_b[1], False, chunk_rows=128)[0]
+    np.testing.assert_allclose(chunked if got.ndim == 2 else chunked[:, 0], got, rtol=0, atol=1e-12 * scale)
+    again = g.predict(Xq)
+    np.testing.assert_array_equal(again, got)                          # fixed reduction order: run-to-run identical

@@ -13,6 +13,10 @@ cudaError_t gpk_launch_lml_grad(const double*, int, int, const GpkKernelParams&,
 cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*, int, const double*, const double*,
                                     double*, cudaStream_t);
 cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
+int gpk_mean_fused_splits(int MP, int N);
+cudaError_t gpk_launch_predict_mean_fused(const double*, int, int, const double*, int, int, const GpkKernelParams&,
+                                          const double*, int, const double*, const double*, double*, double*,
+                                          cudaStream_t);
 cudaError_t gpk_launch_small_rowsumsq(const double*, int, const double*, int, double*, cudaStream_t);
 // Query batches this small take the mat-vec variance path: it re-reads L^-1 once per 8 rows, the DMMA contraction
 // pads to 128 rows and runs on NP/128 CTAs only, so the cross-over moves with N (measured at N=1000 and 20000).
@@ -21,7 +25,7 @@ cudaError_t gpk_launch_extract_lower(const double*, int, double*, int, cudaStrea
 cudaError_t gpk_launch_pad_copy(const double*, int, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_copy_diag(const double*, int, int, double*, cudaStream_t);
 cudaError_t gpk_launch_potrf_inv(double*, int, double*, double*, int, int, int*, cudaStream_t);
-cudaError_t gpk_launch_potrf_inv_ex(double*, int, double*, double*, int, int, int*, cudaStream_t, bool);
+cudaError_t gpk_launch_potrf_inv_ex(double*, int, double*, double*, int, int, int*, cudaStream_t, bool keep_L);
 cudaError_t gpk_launch_lauum(const double*, int, double*, int, int, cudaStream_t);
 cudaError_t gpk_launch_trimv(const double*, int, int, const double*, int, double*, int, int, int, cudaStream_t);
 cudaError_t gpk_launch_dmma_probe(int, int, double*, cudaStream_t);
@@ -67,7 +71,6 @@ int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, 
 int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream) {
   if (!A_d) return -1; if (!Mlow_d) return -2; if (!Mup_d) return -3; if (NP < GPK_TILE || NP % GPK_TILE) return -4;
   if (!info_d) return -5;
-  gpk_i8_invalidate();
   GPK_CHECK(gpk_launch_potrf_inv(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, (cudaStream_t)stream));
   return 0;
 }
@@ -116,17 +119,13 @@ int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double
   if (!ws_d) return -17; if (!out_d) return -18; if (!info_d) return -19;
   const size_t nt = (size_t)NP / 64;
   double* diag = ws_d + nt * nt * (size_t)(gpk_dp_of(D) + 2);
-  gpk_i8_invalidate();
   GPK_CHECK(gpk_launch_gram(X_d, N, D, p, A_d, NP, 1, st));
-  GPK_CHECK(gpk_launch_potrf_inv_ex(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st, (gpk_i8_mode() & 4) != 0));
+  GPK_CHECK(gpk_launch_potrf_inv_ex(A_d, NP, Mlow_d, Mup_d, NP, NP, info_d, st, /*keep_L=*/false));
   GPK_CHECK(gpk_launch_trimv(Mlow_d, NP, NP, y_d, T, u_d, T, 0, T, st));
   GPK_CHECK(gpk_launch_trimv(Mup_d, NP, NP, u_d, T, alpha_d, T, 1, T, st));
   GPK_CHECK(gpk_launch_copy_diag(A_d, NP, NP, diag, st));
   if (with_grad) {
-    // opt-in (gpk_i8_configure, mode bit 1): K^-1 from int8 slice planes on the tcgen05 pipe; 0 = not taken
-    const int took = gpk_i8_mode() ? gpk_i8_try_lauum(Mup_d, NP, A_d, NP, NP, st) : 0;
-    if (took < 0) return took;
-    if (!took) GPK_CHECK(gpk_launch_lauum(Mup_d, NP, A_d, NP, NP, st));
+    GPK_CHECK(gpk_launch_lauum(Mup_d, NP, A_d, NP, NP, st));
   }
   p.jitter = 0.0;
   GPK_CHECK(gpk_launch_lml_grad(X_d, N, D, p, diag, 1, y_d, alpha_d, T, A_d, NP, with_grad, ws_d, out_d, st));
@@ -162,21 +161,36 @@ int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, in
     GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / 32, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
     return 0;
   }
-  const int took = gpk_i8_mode() ? gpk_i8_try_predict_rowsq(Ks_d, MP, Mlow_d, NP, rowsq_d, (cudaStream_t)stream) : 0;
-  if (took < 0) return took;
-  if (!took) {
-    GpkGemmArgs g{};
-    g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
-    g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
-    GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
-  }
+  GpkGemmArgs g{};
+  g.A = Ks_d; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+  g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq_d;
+  GPK_CHECK(gpk_launch_gemm_nt(g, (cudaStream_t)stream));
   GPK_CHECK(gpk_launch_predict_std(rowsq_d, NP / GPK_ROWSQ_TILE, Mq, prior, y_std_d, T, std_d, neg_d, (cudaStream_t)stream));
   return 0;
 }
 
+size_t gpk_predict_mean_workspace_doubles(int MP, int N, int D, int T) {
+  if (MP < 1 || MP % 64 || N < 1 || D < 1 || T < 1) return 0;
+  return (size_t)MP * D + (size_t)MP * T + (size_t)gpk_mean_fused_splits(MP, N) * MP * T + 2;
+}
 size_t gpk_predict_workspace_doubles(int MP, int NP, int D, int T) {
   if (MP < 1 || NP < 1 || D < 1 || T < 1) return 0;
-  return (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_ROWSQ_TILE) + 2;
+  const size_t full = (size_t)MP * NP + (size_t)MP * D + 2 * (size_t)MP * T + (size_t)MP * (NP / GPK_ROWSQ_TILE) + 2;
+  const size_t mean_only = gpk_predict_mean_workspace_doubles(MP, NP, D, T);   // a scratch sized here serves both
+  return full > mean_only ? full : mean_only;
+}
+
+int gpk_predict_mean_fused(const double* Xq_d, int Mq, int MP, const double* X_d, int N, int D, const double* inv_ls_h,
+                           double c, const double* alpha_d, int T, const double* y_mean_d, const double* y_std_d,
+                           double* partial_d, double* mean_d, void* stream) {
+  GpkKernelParams p;
+  if (!Xq_d) return -1; if (Mq < 1) return -2; if (MP % 64 || MP < Mq) return -3; if (!X_d) return -4; if (N < 1) return -5;
+  if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -6;
+  if (!alpha_d) return -9; if (T < 1) return -10; if (!y_mean_d) return -11; if (!y_std_d) return -12;
+  if (!partial_d) return -13; if (!mean_d) return -14;
+  GPK_CHECK(gpk_launch_predict_mean_fused(Xq_d, Mq, MP, X_d, N, D, p, alpha_d, T, y_mean_d, y_std_d, partial_d, mean_d,
+                                          (cudaStream_t)stream));
+  return 0;
 }
 
 // one model's share of a host-to-host predict: everything up to (not including) the device->host copies
@@ -189,9 +203,20 @@ static int predict_enqueue(const double* Xq_h, int Mq, int D, const double* X_d,
   if (NP % GPK_TILE || NP < N) return -12;
   if (T < 1) return -10;
   const int MP = ((Mq + GPK_TILE - 1) / GPK_TILE) * GPK_TILE;
-  if (ws_doubles < gpk_predict_workspace_doubles(MP, NP, D, T)) return -19;
   GpkKernelParams p;
   if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -3;
+  if (!want_std) {
+    // mean only (evaluate_gp_offline.py:198, gp_enhanced_mpc.py:165,175): the fused kernel, no M x N cross-Gram in HBM
+    if (ws_doubles < gpk_predict_mean_workspace_doubles(MP, N, D, T)) return -19;
+    double* xq = ws_d;
+    double* mean_d = xq + (size_t)MP * D;
+    double* partial = mean_d + (size_t)MP * T;
+    GPK_CHECK(cudaMemcpyAsync(xq, Xq_h, sizeof(double) * (size_t)Mq * D, cudaMemcpyHostToDevice, st));
+    GPK_CHECK(gpk_launch_predict_mean_fused(xq, Mq, MP, X_d, N, D, p, alpha_d, T, y_mean_d, y_std_d, partial, mean_d, st));
+    *mean_d_out = mean_d; *std_d_out = nullptr; *neg_d_out = nullptr;
+    return 0;
+  }
+  if (ws_doubles < gpk_predict_workspace_doubles(MP, NP, D, T)) return -19;
   double* Ks = ws_d;
   double* xq = Ks + (size_t)MP * NP;
   double* mean_d = xq + (size_t)MP * D;
@@ -207,14 +232,10 @@ static int predict_enqueue(const double* Xq_h, int Mq, int D, const double* X_d,
       GPK_CHECK(gpk_launch_small_rowsumsq(Mlow_d, NP, Ks, Mq, rowsq, st));
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / 32, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     } else {
-      const int took = gpk_i8_mode() ? gpk_i8_try_predict_rowsq(Ks, MP, Mlow_d, NP, rowsq, st) : 0;
-      if (took < 0) return took;
-      if (!took) {
-        GpkGemmArgs g{};
-        g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
-        g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
-        GPK_CHECK(gpk_launch_gemm_nt(g, st));
-      }
+      GpkGemmArgs g{};
+      g.A = Ks; g.lda = NP; g.B = Mlow_d; g.ldb = NP; g.C = nullptr; g.ldc = 0; g.M = MP; g.N = NP; g.K = NP;
+      g.alpha = 1.0; g.b_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_ROWSUMSQ; g.rowsq = rowsq;
+      GPK_CHECK(gpk_launch_gemm_nt(g, st));
       GPK_CHECK(gpk_launch_predict_std(rowsq, NP / GPK_ROWSQ_TILE, Mq, c + noise, y_std_d, T, std_d, neg_d, st));
     }
   }

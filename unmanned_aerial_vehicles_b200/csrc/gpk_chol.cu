@@ -5,11 +5,12 @@
 //   potrf + trtri (2N^3/3) followed by lauum (N^3/3), all as large-K NT GEMMs on the FP64 tensor pipe.
 //
 // Buffers (NP x NP, NP % 128 == 0):
-//   A    : in  = lower triangle of K (+ identity padding), out = lower Cholesky factor L
+//   A    : in  = lower triangle of K (+ identity padding), out = lower Cholesky factor L; the strictly upper
+//          128-blocks are scratch (each level parks its Wt product there)
 //   Mlow : out = L^-1 (lower; diagonal 128-blocks carry explicit zeros above the diagonal)
 //   Mup  : out = L^-T (upper; = Mlow transposed)
 // Recursion on [off, off+n):  n1 | n2 split at a multiple of 128
-//   rec(11);  L21 = A21 * M11^T;  A22 -= L21 L21^T;  rec(22);  M21 = -M22 * L21 * M11.
+//   rec(11);  L21 = A21 * M11^T;  A22 -= L21 L21^T;  rec(22);  M21 = -M22 * L21 * M11  (details at chol_rec).
 #include "gpk_common.cuh"
 
 // ---------------------------------------------------------------------------------------------------------
@@ -351,14 +352,16 @@ static cudaError_t chol_side_init(CholSide& cs) {
 }
 
 struct CholCtx { double* A; int lda; double* Ml; double* Mu; int ldm; int* info; cudaStream_t st; cudaError_t err;
-                 CholSide* side; bool i8_tail; };
+                 CholSide* side; bool keep_L; };
 
-static inline cudaError_t i8_rc_to_cuda(int rc) { return rc <= -1000 ? (cudaError_t)(-rc - 1000) : cudaErrorInvalidValue; }
-
-// rm: this node lies on the right-most path of the recursion (root, root.22, root.22.22, ...).  The two inverse
-// products of such a node are read by no later L21 -- only by K^-1 and predict -- so with the opt-in int8 tail
-// (CholCtx::i8_tail) they may run on the tcgen05 pipe; i8_off is this node's scratch offset.
-static void chol_rec(CholCtx& c, int off, int n, int depth = 0, bool rm = true, size_t i8_off = 0) {
+// One node of the recursion on [off, off+n), split n1 | n2 at a multiple of 128:
+//   rec(11);  L21 = A21 M11^T -> Mlow21;  [side stream] Wt = M11^T-part * L21^T -> A12 (scratch: the strictly upper
+//   part of A is never read);  A22 -= L21 L21^T;  rec(22);  M21 = -M22 Wt^T -> Mlow21 AND, transposed by the same
+//   GEMM's epilogue, Mup12.
+// L21 is consumed where the GEMM left it (Mlow21) and is copied over A21 only when the caller wants L itself
+// (keep_L: the final factorisation, whose L_ the estimator may download); an objective evaluation needs only L's
+// diagonal (log-det), which the leaves leave in A.
+static void chol_rec(CholCtx& c, int off, int n, int depth = 0) {
   if (c.err != cudaSuccess) return;
   if (n <= GPK_TILE) {
     if ((c.err = leaf_configure()) != cudaSuccess) return;
@@ -367,71 +370,63 @@ static void chol_rec(CholCtx& c, int off, int n, int depth = 0, bool rm = true, 
     return;
   }
   const int n1 = GPK_TILE * ((n / GPK_TILE + 1) / 2), n2 = n - n1, o2 = off + n1;
-  chol_rec(c, off, n1, depth + 1, false, 0);
+  chol_rec(c, off, n1, depth + 1);
   if (c.err != cudaSuccess) return;
-  const bool tail = c.i8_tail && rm;
   double* A21 = c.A + (size_t)o2 * c.lda + off;
+  double* A12 = c.A + (size_t)off * c.lda + o2;      // scratch for Wt (n1 x n2)
   double* Ml21 = c.Ml + (size_t)o2 * c.ldm + off;
   double* Mu12 = c.Mu + (size_t)off * c.ldm + o2;
   GpkGemmArgs g{};
-  // L21 = A21 * M11^T  (tmp in Mlow21, then copied over A21)
+  // L21 = A21 * M11^T -> Mlow21
   g.A = A21; g.lda = c.lda; g.B = c.Ml + (size_t)off * c.ldm + off; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
   g.M = n2; g.N = n1; g.K = n1; g.alpha = 1.0; g.accumulate = 0; g.a_tri = GPK_TRI_NONE; g.b_tri = GPK_TRI_LOWER;
   g.lower_only = 0; g.epilogue = GPK_EPI_STORE; g.rowsq = nullptr;
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
-  if ((c.err = gpk_launch_copy_block(Ml21, c.ldm, A21, c.lda, n2, n1, c.st)) != cudaSuccess) return;
-  // Wt = Mt11 * L21^T  -> Mup12 (n1 x n2): independent of the A22 update and of rec(22) -> side stream
+  if (c.keep_L && (c.err = gpk_launch_copy_block(Ml21, c.ldm, A21, c.lda, n2, n1, c.st)) != cudaSuccess) return;
+  // Wt = Mt11 * L21^T -> A12: independent of the A22 update and of rec(22) -> side stream
   const bool fork = c.side != nullptr && depth < GPK_CHOL_MAXDEPTH;
   cudaStream_t ws = fork ? c.side->side[depth] : c.st;
   if (fork) {
-    if ((c.err = cudaEventRecord(c.side->fork, c.st)) != cudaSuccess) return;    // after the L21 copy above
+    if ((c.err = cudaEventRecord(c.side->fork, c.st)) != cudaSuccess) return;    // after L21 above
     if ((c.err = cudaStreamWaitEvent(ws, c.side->fork, 0)) != cudaSuccess) return;
   }
   GpkGemmArgs w{};
-  w.A = c.Mu + (size_t)off * c.ldm + off; w.lda = c.ldm; w.B = A21; w.ldb = c.lda; w.C = Mu12; w.ldc = c.ldm;
+  w.A = c.Mu + (size_t)off * c.ldm + off; w.lda = c.ldm; w.B = Ml21; w.ldb = c.ldm; w.C = A12; w.ldc = c.lda;
   w.M = n1; w.N = n2; w.K = n1; w.alpha = 1.0; w.a_tri = GPK_TRI_UPPER; w.epilogue = GPK_EPI_STORE;
-  auto launch_w = [&](cudaStream_t s) -> cudaError_t {
-    if (tail) {
-      const int took = gpk_i8_try_gemm(w.A, w.lda, w.a_tri, w.B, w.ldb, w.b_tri, w.M, w.N, w.K, w.alpha, w.C, w.ldc, i8_off, s);
-      if (took < 0) return i8_rc_to_cuda(took);
-      if (took) return cudaSuccess;
-    }
-    return gpk_launch_gemm_nt(w, s);
-  };
   if (fork) {
-    if ((c.err = launch_w(ws)) != cudaSuccess) return;
+    if ((c.err = gpk_launch_gemm_nt(w, ws)) != cudaSuccess) return;
     if ((c.err = cudaEventRecord(c.side->join[depth], ws)) != cudaSuccess) return;
   }
   // A22 -= L21 L21^T (lower tiles)
   g = GpkGemmArgs{};
-  g.A = A21; g.lda = c.lda; g.B = A21; g.ldb = c.lda; g.C = c.A + (size_t)o2 * c.lda + o2; g.ldc = c.lda;
+  g.A = Ml21; g.lda = c.ldm; g.B = Ml21; g.ldb = c.ldm; g.C = c.A + (size_t)o2 * c.lda + o2; g.ldc = c.lda;
   g.M = n2; g.N = n2; g.K = n1; g.alpha = -1.0; g.accumulate = 1; g.lower_only = 1; g.epilogue = GPK_EPI_STORE;
   if ((c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
-  chol_rec(c, o2, n2, depth + 1, rm, tail ? i8_off + gpk_i8_pair_bytes(n1, n2, n1) : 0);
+  chol_rec(c, o2, n2, depth + 1);
   if (c.err != cudaSuccess) return;
   if (fork) {
     if ((c.err = cudaStreamWaitEvent(c.st, c.side->join[depth], 0)) != cudaSuccess) return;
   } else {
-    if ((c.err = launch_w(c.st)) != cudaSuccess) return;
+    if ((c.err = gpk_launch_gemm_nt(w, c.st)) != cudaSuccess) return;
   }
-  // M21 = -M22 * W  : C[m,j] = -sum_k M22[m,k] Wt[j,k]
+  // M21 = -M22 * W : C[m,j] = -sum_k M22[m,k] Wt[j,k] -> Mlow21, and its transpose -> Mup12 from the same epilogue
   g = GpkGemmArgs{};
-  g.A = c.Ml + (size_t)o2 * c.ldm + o2; g.lda = c.ldm; g.B = Mu12; g.ldb = c.ldm; g.C = Ml21; g.ldc = c.ldm;
+  g.A = c.Ml + (size_t)o2 * c.ldm + o2; g.lda = c.ldm; g.B = A12; g.ldb = c.lda; g.C = Ml21; g.ldc = c.ldm;
   g.M = n2; g.N = n1; g.K = n2; g.alpha = -1.0; g.a_tri = GPK_TRI_LOWER; g.epilogue = GPK_EPI_STORE;
-  int took = 0;
-  if (tail) {   // the planes of this node's first product are dead by now (joined above): same region
-    took = gpk_i8_try_gemm(g.A, g.lda, g.a_tri, g.B, g.ldb, g.b_tri, g.M, g.N, g.K, g.alpha, g.C, g.ldc, i8_off, c.st);
-    if (took < 0) { c.err = i8_rc_to_cuda(took); return; }
-  }
-  if (!took && (c.err = gpk_launch_gemm_nt(g, c.st)) != cudaSuccess) return;
-  c.err = gpk_launch_transpose_block(Ml21, c.ldm, Mu12, c.ldm, n2, n1, c.st);
+  g.Ct = Mu12; g.ldct = c.ldm;
+  c.err = gpk_launch_gemm_nt(g, c.st);
 }
 
-// i8_tail: objective evaluations only (gpk_lml_eval, opt-in mode bit 4); the final factorisation predict reads
-// (gpk_potrf_inv) always keeps an all-FP64 inverse.
+// The side streams and the fork/join events are per device: one enqueue at a time per device (two host threads
+// factoring on the same GPU would otherwise re-record the fork event between the other's record and wait).
+#include <mutex>
+static std::mutex g_chol_mu[GPK_MAX_DEV];
+
+// keep_L = false: objective evaluations (gpk_lml_eval) -- A ends with L's diagonal 128-blocks only.
 cudaError_t gpk_launch_potrf_inv_ex(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
-                                    cudaStream_t st, bool i8_tail) {
+                                    cudaStream_t st, bool keep_L) {
   if (NP % GPK_TILE) return cudaErrorInvalidValue;
+  std::lock_guard<std::mutex> lock(g_chol_mu[gpk_current_device()]);
   cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
   // the side stream is bypassed while per-launch GEMM timing is on (overlapped durations would not add up)
@@ -440,14 +435,14 @@ cudaError_t gpk_launch_potrf_inv_ex(double* A, int lda, double* Mlow, double* Mu
     side = &g_cs[gpk_current_device()];
     if ((e = chol_side_init(*side)) != cudaSuccess) return e;
   }
-  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side, i8_tail};
+  CholCtx c{A, lda, Mlow, Mup, ldm, info, st, cudaSuccess, side, keep_L};
   chol_rec(c, 0, NP);
   return c.err;
 }
 
 cudaError_t gpk_launch_potrf_inv(double* A, int lda, double* Mlow, double* Mup, int ldm, int NP, int* info,
                                  cudaStream_t st) {
-  return gpk_launch_potrf_inv_ex(A, lda, Mlow, Mup, ldm, NP, info, st, false);
+  return gpk_launch_potrf_inv_ex(A, lda, Mlow, Mup, ldm, NP, info, st, true);
 }
 
 // K^-1 = L^-T L^-1 = Mup * Mup^T  (lower tiles of Kinv are written; diagonal tiles in full)

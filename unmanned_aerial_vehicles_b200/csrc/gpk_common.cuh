@@ -42,6 +42,7 @@ struct GpkGemmArgs {
   int epilogue;               // GPK_EPI_*
   double* rowsq;              // GPK_EPI_ROWSUMSQ: (M x N/GPK_TILE) partial row sums of squares
   int raster_rows;            // tile-rows per raster group; 0 = the launcher's default (8, or GPK_GEMM_RASTER)
+  double* Ct; int ldct;       // GPK_EPI_STORE, optional: the result is ALSO stored transposed, Ct (N x M) row-major
 };
 
 // internal launchers (C++ linkage), all asynchronous on `st`
@@ -52,16 +53,6 @@ cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, 
 // per-device one-time state (function attributes, side streams): indexed by the current device ordinal
 #define GPK_MAX_DEV 64
 static inline int gpk_current_device() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < GPK_MAX_DEV) ? d : 0; }
-
-// opt-in int8 (tcgen05) contraction, gpk_i8gemm.cu: per-device registered scratch and what it may be used for
-struct GpkI8State { char* ws; size_t bytes; int NP, MPmax, S, mode; const double* prepared; };
-extern "C" int gpk_i8_mode();            // 0 unless gpk_i8_configure() enabled something on the current device
-extern "C" void gpk_i8_invalidate();     // the L^-1 whose planes were prepared for predict is about to change
-int gpk_i8_try_lauum(const double* Mup, int ldm, double* Kinv, int ldk, int NP, cudaStream_t st);
-int gpk_i8_try_gemm(const double* A, int lda, int a_tri, const double* B, int ldb, int b_tri, int M, int N, int K,
-                    double alpha, double* C, int ldc, size_t region_off, cudaStream_t st);
-size_t gpk_i8_pair_bytes(int M, int N, int K);   // scratch one gpk_i8_try_gemm takes from its region (0: tail mode off)
-int gpk_i8_try_predict_rowsq(const double* Ks, int MP, const double* Mlow, int NP, double* rowsq, cudaStream_t st);
 
 extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)
 #define GPK_LAUNCHED() (++g_gpk_launches)

@@ -2,7 +2,9 @@
 //   C (+)= alpha * A * B^T,  A (M x K), B (N x K), C (M x N), all row-major, dims % 128 == 0.
 // Replaces the OpenBLAS dgemm/dsyrk/dtrsm/dtrmm calls hidden under scipy.linalg.cholesky /
 // cho_solve / solve_triangular (sklearn/gaussian_process/_gpr.py:352,363,460,591,601,631).
-// CTA tile 128x128, k-tile 16, 3-stage cp.async pipeline, 8 warps (2 x 4), warp tile 64 x 32.
+// One kernel template, three CTA tiles: 64x64 (4 warps, warp tile 32x32; the default), 32x32 (small or triangular
+// products that would leave SMs idle) and 128x128 (8 warps; kept for sweeps, not selected); k-tile 32, 2-stage
+// cp.async ring, padded shared-memory rows (stride k-tile + 4 doubles: conflict-free 8x4 DMMA fragment reads).
 #include "gpk_common.cuh"
 #include <stdlib.h>
 
@@ -138,6 +140,10 @@ __global__ void __launch_bounds__(32 * WR * WC, (TS == 128) ? 1 : 2) gpk_gemm_nt
         double2 v = make_double2(g.alpha * acc[i][j][0], g.alpha * acc[i][j][1]);
         if (g.accumulate) { double2 o = *p; v.x += o.x; v.y += o.y; }
         *p = v;
+        if (g.Ct) {   // transposed copy: the 8 lanes that share fk write 8 consecutive doubles (one 64-byte segment)
+          g.Ct[(size_t)col * g.ldct + row] = v.x;
+          g.Ct[(size_t)(col + 1) * g.ldct + row] = v.y;
+        }
       }
     }
   } else if (TS == GPK_ROWSQ_TILE) {  // GPK_EPI_ROWSUMSQ: rowsq[row, tn] = sum_n (alpha*acc)^2 over this tile's columns
@@ -246,8 +252,8 @@ double gpk_profile_collect() {
 // ---- small data-movement helpers ---------------------------------------------------------
 __global__ void gpk_copy_block_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int ldd,
                                       int rows, int cols) {
-  int c = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
-  int r = blockIdx.y;
+  int c = (blockIdx.y * blockDim.x + threadIdx.x) * 2;
+  int r = blockIdx.x;   // rows in grid.x: no 65535 limit
   if (c < cols)
     *reinterpret_cast<double2*>(dst + (size_t)r * ldd + c) =
         *reinterpret_cast<const double2*>(src + (size_t)r * lds + c);
@@ -255,7 +261,7 @@ __global__ void gpk_copy_block_kernel(const double* __restrict__ src, int lds, d
 cudaError_t gpk_launch_copy_block(const double* src, int lds, double* dst, int ldd, int rows, int cols,
                                   cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
-  dim3 grid((cols / 2 + 255) / 256, rows);
+  dim3 grid(rows, (cols / 2 + 255) / 256);
   gpk_copy_block_kernel<<<grid, 256, 0, st>>>(src, lds, dst, ldd, rows, cols); GPK_LAUNCHED();
   return cudaGetLastError();
 }

@@ -212,6 +212,81 @@ __global__ void gpk_predict_mean_kernel(const double* __restrict__ Ks, int ldk, 
   }
 }
 
+// Mean-only predict, fused (sklearn _gpr.py:446-454 with return_std=False; what evaluate_gp_offline.py:198 and
+// gp_enhanced_mpc.py:165,175 call): mean[q,t] = y_mean[t] + y_std[t] * sum_j c*exp(-1/2 |xq - x_j|^2_l) alpha[j,t].
+// The cross-Gram row is consumed as it is produced and never stored: no M x N pass through HBM at all (the two-pass
+// route writes and re-reads 8*M*N bytes).  Bound by FP64 exp + FMA issue: per (query, training row) pair 2*DP
+// operations for the distance, ~25 for exp, TT for the accumulation; algorithmic HBM bytes per query 8*(D + T).
+// CTA = 64 query rows x one slice of the training rows (blockIdx.y of `nsplit`), 64 training rows per step staged in
+// shared memory with the alpha rows that go with them.  Thread (ty, tx) of a 32 x 8 grid keeps its two query rows
+// (ty, ty+32) in registers and walks training rows tx+8b of the step (cyclic: lanes read shared memory with an odd row
+// stride, conflict-free; the 8 tx lanes that share a query row are reduced with shuffles, fixed order).  partial[(split*MP + q)*T + t]; a second tiny kernel adds
+// the splits in order and applies the target scale: no atomics, so a given (MP, N) always sums in the same order.
+template <int DP, int TT>
+__global__ void __launch_bounds__(256, 2) gpk_predict_mean_fused_kernel(
+    const double* __restrict__ Xq, int ldq, int Mq, const double* __restrict__ X, int ldx, int N, GpkKernelParams p,
+    const double* __restrict__ alpha, int lda, int t0, int T, double* __restrict__ partial, int MP, int tiles_per_split) {
+  __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1], aj[KTILE][TT + 1];
+  const int tid = threadIdx.x, tx = tid & 7, ty = tid >> 3;      // 32 x 8 threads: query rows ty, ty+32; columns tx+8b
+  const int i0 = blockIdx.x * KTILE, split = blockIdx.y;
+  const int ntiles = (N + KTILE - 1) / KTILE;
+  const int jt0 = split * tiles_per_split, jt1 = min(ntiles, jt0 + tiles_per_split);
+  load_scaled_rows<DP>(xi, Xq, ldq, i0, Mq, p, tid);
+  __syncthreads();
+  double xq0[DP], xq1[DP], acc0[TT], acc1[TT];
+#pragma unroll
+  for (int d = 0; d < DP; ++d) { xq0[d] = xi[ty][d]; xq1[d] = xi[ty + 32][d]; }
+#pragma unroll
+  for (int t = 0; t < TT; ++t) acc0[t] = acc1[t] = 0.0;
+  for (int jt = jt0; jt < jt1; ++jt) {
+    const int j0 = jt * KTILE;
+    __syncthreads();                       // the previous step's xj / aj are no longer read
+    load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
+    for (int idx = tid; idx < KTILE * TT; idx += 256) {
+      const int r = idx / TT, t = idx % TT;
+      aj[r][t] = (j0 + r < N && t0 + t < T) ? alpha[(size_t)(j0 + r) * lda + t0 + t] : 0.0;   // padding rows add 0
+    }
+    __syncthreads();
+#pragma unroll 2
+    for (int b = 0; b < 8; ++b) {
+      const int lj = tx + 8 * b;
+      double d20 = 0.0, d21 = 0.0;
+#pragma unroll
+      for (int d = 0; d < DP; ++d) {
+        const double x = xj[lj][d], f0 = xq0[d] - x, f1 = xq1[d] - x;
+        d20 += f0 * f0; d21 += f1 * f1;
+      }
+      const double k0 = exp(-0.5 * d20), k1 = exp(-0.5 * d21);
+#pragma unroll
+      for (int t = 0; t < TT; ++t) {
+        const double av = aj[lj][t];
+        acc0[t] = fma(k0, av, acc0[t]); acc1[t] = fma(k1, av, acc1[t]);
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < TT; ++t) {
+    double s0 = acc0[t], s1 = acc1[t];
+#pragma unroll
+    for (int o = 4; o; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o, 8); s1 += __shfl_xor_sync(0xffffffffu, s1, o, 8); }
+    if (tx == 0 && t0 + t < T) {
+      partial[((size_t)split * MP + i0 + ty) * T + t0 + t] = p.c * s0;
+      partial[((size_t)split * MP + i0 + ty + 32) * T + t0 + t] = p.c * s1;
+    }
+  }
+}
+// mean[q,t] = (sum_split partial) * y_std[t] + y_mean[t]
+__global__ void gpk_predict_mean_finish_kernel(const double* __restrict__ partial, int nsplit, int MP, int Mq, int T,
+                                               const double* __restrict__ y_mean, const double* __restrict__ y_std,
+                                               double* __restrict__ mean) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= Mq * T) return;
+  const int t = idx % T;
+  double s = 0.0;
+  for (int k = 0; k < nsplit; ++k) s += partial[(size_t)k * MP * T + idx];
+  mean[idx] = s * y_std[t] + y_mean[t];
+}
+
 // Few query rows (control-tick calls): one CTA per row, so a single row at N=20k is spread over 8 warps
 // (the warp-per-row kernel above takes 0.31 ms for it).  Fixed reduction order -> deterministic.
 __global__ void __launch_bounds__(256) gpk_predict_mean_cta_kernel(const double* __restrict__ Ks, int ldk, int N,
@@ -323,14 +398,14 @@ cudaError_t gpk_launch_small_rowsumsq(const double* Mlow, int NP, const double* 
 
 // dst (N x N, ld N) = lower triangle of src's leading N x N block, zeros above (scipy's L_ layout)
 __global__ void gpk_extract_lower_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int N) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  int c = blockIdx.y * blockDim.x + threadIdx.x, r = blockIdx.x;   // rows in grid.x: no 65535 limit (N > 65535)
   if (c < N) dst[(size_t)r * N + c] = (c <= r) ? src[(size_t)r * lds + c] : 0.0;
 }
 
 // zero-pad copy: dst (RP x ldd) <- src (R x C), rest zero
 __global__ void gpk_pad_copy_kernel(const double* __restrict__ src, int lds, int R, int C, double* __restrict__ dst,
                                     int ldd, int RP, int CP) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  int c = blockIdx.y * blockDim.x + threadIdx.x, r = blockIdx.x;   // rows in grid.x: no 65535 limit
   if (c < CP && r < RP) dst[(size_t)r * ldd + c] = (r < R && c < C) ? src[(size_t)r * lds + c] : 0.0;
 }
 
@@ -339,12 +414,13 @@ __global__ void gpk_pad_copy_kernel(const double* __restrict__ src, int lds, int
   do {                                             \
     if ((D) <= 4) { CALL(4); }                     \
     else if ((D) <= 8) { CALL(8); }                \
+    else if ((D) <= 10) { CALL(10); }              \
     else if ((D) <= 12) { CALL(12); }              \
     else if ((D) <= 16) { CALL(16); }              \
     else { CALL(32); }                             \
   } while (0)
 
-int gpk_dp_of(int D) { return D <= 4 ? 4 : D <= 8 ? 8 : D <= 12 ? 12 : D <= 16 ? 16 : 32; }
+int gpk_dp_of(int D) { return D <= 4 ? 4 : D <= 8 ? 8 : D <= 10 ? 10 : D <= 12 ? 12 : D <= 16 ? 16 : 32; }
 
 cudaError_t gpk_launch_gram(const double* X, int N, int D, const GpkKernelParams& p, double* K, int NP,
                             int lower_only, cudaStream_t st) {
@@ -395,6 +471,35 @@ cudaError_t gpk_launch_predict_mean(const double* Ks, int Mq, int N, int NP, con
   return cudaGetLastError();
 }
 
+// number of training-row slices the fused mean kernel is split into: enough CTAs for two per SM when there are few
+// query rows (the 25-row control tick), one slice when the query tiles alone fill the GPU
+int gpk_mean_fused_splits(int MP, int N) {
+  const int rowtiles = MP / KTILE, ntiles = (N + KTILE - 1) / KTILE;
+  int ns = (2 * 148 + rowtiles - 1) / rowtiles;
+  if (ns > ntiles) ns = ntiles;
+  return ns < 1 ? 1 : ns;
+}
+// partial: nsplit * MP * T doubles
+cudaError_t gpk_launch_predict_mean_fused(const double* Xq, int Mq, int MP, const double* X, int N, int D,
+                                          const GpkKernelParams& p, const double* alpha, int T, const double* y_mean,
+                                          const double* y_std, double* partial, double* mean, cudaStream_t st) {
+  const int ntiles = (N + KTILE - 1) / KTILE, nsplit = gpk_mean_fused_splits(MP, N);
+  const int tps = (ntiles + nsplit - 1) / nsplit;
+  dim3 grid(MP / KTILE, nsplit);
+  for (int t0 = 0; t0 < T; t0 += 8) {
+    const int tc = T - t0;
+#define CALLF(DPV, TTV) gpk_predict_mean_fused_kernel<DPV, TTV><<<grid, 256, 0, st>>>(Xq, D, Mq, X, D, N, p, alpha, T, t0, T, partial, MP, tps)
+#define CALLD(DPV) do { if (tc <= 4) CALLF(DPV, 4); else CALLF(DPV, 8); } while (0)
+    if (D <= 4) CALLD(4); else if (D <= 8) CALLD(8); else if (D <= 10) CALLD(10); else if (D <= 12) CALLD(12);
+    else if (D <= 16) CALLD(16); else CALLD(32);
+#undef CALLD
+#undef CALLF
+    GPK_LAUNCHED();
+  }
+  gpk_predict_mean_finish_kernel<<<(Mq * T + 255) / 256, 256, 0, st>>>(partial, nsplit, MP, Mq, T, y_mean, y_std, mean); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+
 cudaError_t gpk_launch_predict_std(const double* rowsq, int ntiles, int Mq, double prior, const double* y_std, int T,
                                    double* std_out, int* neg, cudaStream_t st) {
   gpk_predict_std_kernel<<<(Mq + 255) / 256, 256, 0, st>>>(rowsq, ntiles, Mq, prior, y_std, T, std_out, T, neg); GPK_LAUNCHED();
@@ -402,13 +507,13 @@ cudaError_t gpk_launch_predict_std(const double* rowsq, int ntiles, int Mq, doub
 }
 
 cudaError_t gpk_launch_extract_lower(const double* src, int NP, double* dst, int N, cudaStream_t st) {
-  dim3 grid((N + 255) / 256, N);
+  dim3 grid(N, (N + 255) / 256);
   gpk_extract_lower_kernel<<<grid, 256, 0, st>>>(src, NP, dst, N); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
 cudaError_t gpk_launch_pad_copy(const double* src, int R, int C, double* dst, int RP, int CP, cudaStream_t st) {
-  dim3 grid((CP + 127) / 128, RP);
+  dim3 grid(RP, (CP + 127) / 128);
   gpk_pad_copy_kernel<<<grid, 128, 0, st>>>(src, C, R, C, dst, CP, RP, CP); GPK_LAUNCHED();
   return cudaGetLastError();
 }

@@ -57,6 +57,9 @@ class CudaOps:
         self.info = torch.zeros(1, dtype=torch.int32, device=self.dev)
         self.groups = {"world": group, "row": None, "col": None}
         self.side_stream = torch.cuda.Stream(device=self.dev)
+        self.bcast_bytes = 0          # bytes this rank sent or received through broadcasts (NCCL traffic of the path)
+        self.bcast_calls = 0
+        self.trace = None             # list of (phase, panel, start event, end event) while tracing
 
     def _st(self):
         return C.c_void_p(self.t.cuda.current_stream().cuda_stream)
@@ -149,7 +152,34 @@ class CudaOps:
         g = self.groups[kind]
         if kind != "world" and g is None:
             return                      # group of one
+        self.bcast_bytes += buf.numel() * 8
+        self.bcast_calls += 1
         self.dist.broadcast(buf, src=src, group=g)
+
+    @contextlib.contextmanager
+    def span(self, phase, k):
+        """CUDA-event pair around the enclosed launches on the current stream (only while self.trace is a list)"""
+        if self.trace is None:
+            yield
+            return
+        st = self.t.cuda.current_stream()
+        e0, e1 = self.t.cuda.Event(enable_timing=True), self.t.cuda.Event(enable_timing=True)
+        e0.record(st)
+        try:
+            yield
+        finally:
+            e1.record(st)
+            self.trace.append((phase, k, e0, e1))
+
+    def trace_summary(self):
+        """seconds per phase (summed over panels) from the recorded spans; synchronises"""
+        self.t.cuda.synchronize()
+        out = {}
+        for phase, k, e0, e1 in self.trace or []:
+            d = out.setdefault(phase, {"seconds": 0.0, "spans": 0, "max_ms": 0.0})
+            ms = e0.elapsed_time(e1)
+            d["seconds"] += ms * 1e-3; d["spans"] += 1; d["max_ms"] = max(d["max_ms"], ms)
+        return out
 
     def allreduce_sum(self, buf):
         if self._multi():
@@ -230,6 +260,10 @@ class DistGP:
         self.gemm_flops = 0.0
         self.factored = False
 
+    def _span(self, phase, k=-1):
+        sp = getattr(self.ops, "span", None)
+        return sp(phase, k) if sp is not None else contextlib.nullcontext()
+
     # -- index helpers --------------------------------------------------------------------------------
     def lfirst(self, m):
         """number of this rank's row tiles with global index < m (= local index of the first owned row >= m)"""
@@ -273,16 +307,19 @@ class DistGP:
         Ck = self.cols[k]
         own_diag = self.pr == k % self.Pr
         if own_diag:
-            o.potrf_inv(Ck[:NB], self.Ml[k], self.Mu[k], NB, k)
-            o.copy(self.Ml[k], self.mlbuf)
-        o.bcast(self.mlbuf, self.owner(k), "col")
+            with self._span("diag_potrf_inv", k):
+                o.potrf_inv(Ck[:NB], self.Ml[k], self.Mu[k], NB, k)
+                o.copy(self.Ml[k], self.mlbuf)
+        with self._span("bcast_diag_inverse", k):
+            o.bcast(self.mlbuf, self.owner(k), "col")
         off = NB if own_diag else 0
         rows = Ck.shape[0] - off
         if rows > 0:
             l0 = self.lfirst(k + 1)
             dst = self.Lrow[b][l0 * NB: l0 * NB + rows]
-            o.gemm_nt(Ck[off:], self.mlbuf, dst, rows, NB, NB, 1.0, 0, b_tri=1)
-            o.copy(dst, Ck[off:])
+            with self._span("panel_gemm", k):
+                o.gemm_nt(Ck[off:], self.mlbuf, dst, rows, NB, NB, 1.0, 0, b_tri=1)
+                o.copy(dst, Ck[off:])
             self.gemm_flops += rows * float(NB) * NB
 
     def _panel_bcast(self, k, b):
@@ -290,7 +327,8 @@ class DistGP:
         o, NB, Pr, Pc = self.ops, self.NB, self.Pr, self.Pc
         l0 = self.lfirst(k + 1)
         if self.nlr - l0 > 0:
-            o.bcast(self.Lrow[b][l0 * NB: self.nlr * NB], self.pr * Pc + k % Pc, "row")
+            with self._span("bcast_panel_rows", k):
+                o.bcast(self.Lrow[b][l0 * NB: self.nlr * NB], self.pr * Pc + k % Pc, "row")
         row3 = self.Lrow[b].reshape(-1, NB, NB)
         col3 = self.Lcol[b].reshape(-1, NB, NB)
         for rp in range(Pr):
@@ -298,10 +336,11 @@ class DistGP:
             if not js:
                 continue
             c0, c1 = self.colpos[js[0]], self.colpos[js[-1]] + 1
-            if self.pr == rp:
-                step = (js[1] - js[0]) // Pr if len(js) > 1 else 1
-                o.copy(row3[js[0] // Pr: js[-1] // Pr + 1: step], col3[c0:c1])
-            o.bcast(self.Lcol[b][c0 * NB: c1 * NB], rp * Pc + self.pc, "col")
+            with self._span("bcast_panel_cols", k):
+                if self.pr == rp:
+                    step = (js[1] - js[0]) // Pr if len(js) > 1 else 1
+                    o.copy(row3[js[0] // Pr: js[-1] // Pr + 1: step], col3[c0:c1])
+                o.bcast(self.Lcol[b][c0 * NB: c1 * NB], rp * Pc + self.pc, "col")
 
     def _update(self, k, b, js):
         """A[i >= j, j] -= L[i >= j, k] L[j, k]^T for the owned block columns in js"""
@@ -320,20 +359,24 @@ class DistGP:
         o, NB, nb = self.ops, self.NB, self.nb
         side = o.side if self.lookahead else contextlib.nullcontext
         self.theta = (tuple(float(v) for v in inv_ls), float(c), float(noise))
-        self.assemble(inv_ls, c, noise)
+        with self._span("assemble"):
+            self.assemble(inv_ls, c, noise)
         self._panel_factor(0, 0)
         with side():
             self._panel_bcast(0, 0)
         for k in range(nb):
             b = k % 2
-            o.join_side()                      # panel k has arrived in Lrow[b] / Lcol[b]
+            with self._span("wait_panel", k):  # on the main stream: how long it stalls for panel k's broadcasts
+                o.join_side()                  # panel k has arrived in Lrow[b] / Lcol[b]
             if k + 1 < nb:
                 if self.pc == (k + 1) % self.Pc:
-                    self._update(k, b, [k + 1])
+                    with self._span("update_next_column", k):
+                        self._update(k, b, [k + 1])
                 self._panel_factor(k + 1, 1 - b)
                 with side():                   # overlaps the rest of the trailing update below
                     self._panel_bcast(k + 1, 1 - b)
-            self._update(k, b, [j for j in self.my_cols if j > k + 1])
+            with self._span("update_trailing", k):
+                self._update(k, b, [j for j in self.my_cols if j > k + 1])
         o.join_side()
         infos = o.read_infos()
         bad = [k * NB + int(infos[k]) for k in self.diag if infos[k] != 0]

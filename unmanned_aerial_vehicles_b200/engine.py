@@ -7,7 +7,6 @@ through the C ABI (include/gpk.h).  Mirrors the arithmetic of sklearn/gaussian_p
 from __future__ import annotations
 
 import ctypes as C
-import os
 import threading
 
 import numpy as np
@@ -21,9 +20,6 @@ def _torch_cuda():
     if not torch.cuda.is_available():
         raise _lib.GpkUnavailable("no CUDA device: the GP hot path has no CPU fallback")
     return torch
-
-
-_I8_OWNER = {}   # device index -> (id(engine), scratch pointer) whose int8 scratch libgpk currently holds
 
 
 class DeviceGP:
@@ -72,46 +68,6 @@ class DeviceGP:
             self.A_d = t.empty(shape, dtype=t.float64, device=self.device)
             self.Mlow_d = t.empty(shape, dtype=t.float64, device=self.device)
             self.Mup_d = t.empty(shape, dtype=t.float64, device=self.device)
-            self._configure_i8()
-
-    def _configure_i8(self):
-        """EXPERIMENTAL, off unless GPK_I8 is set (bit 1: K^-1 of the objective, bit 2: predict's variance
-        contraction, bit 4: right-most-path inverse products of the objective; GPK_I8_SLICES, default 7): allocates the scratch libgpk's int8-sliced tcgen05 contraction needs
-        (DESIGN.md section 8).  A shape it cannot take is an error here, not a silent fall back."""
-        self.i8_mode = 0
-        self._i8_planes_ok = False
-        mode = int(os.environ.get("GPK_I8", "0") or 0)
-        if mode == 0:
-            return
-        t = self.torch
-        S = int(os.environ.get("GPK_I8_SLICES", "7"))
-        MPmax = self._chunk_rows_default()
-        nbytes = int(self.lib.gpk_i8_workspace_bytes(self.NP, MPmax, S))
-        if nbytes == 0:
-            raise _lib.GpkError(f"GPK_I8: unsupported shape NP={self.NP} MPmax={MPmax} S={S}")
-        self._i8_ws = t.empty(nbytes, dtype=t.uint8, device=self.device)
-        self._i8_cfg = (nbytes, self.NP, MPmax, S, mode)
-        self.i8_mode = mode
-
-    def _i8_bind(self, need_planes: bool = False):
-        """libgpk keeps ONE registered int8 scratch per device; several engines can live on a device (one per
-        output in PerOutputGP), so each call re-registers its own when another engine's is in place, and predict
-        re-slices L^-1 when its planes were lost that way.  Call inside ``torch.cuda.device(self.device)``."""
-        dev = self.device.index
-        if not getattr(self, "i8_mode", 0):
-            if _I8_OWNER.get(dev) is not None:       # another engine's opt-in must not leak into this one
-                _lib.check(self.lib.gpk_i8_configure(None, 0, 0, 0, 0, 0), "gpk_i8_configure")
-                _I8_OWNER[dev] = None
-            return
-        me = (id(self), self._i8_ws.data_ptr())
-        if _I8_OWNER.get(dev) != me:
-            _lib.check(self.lib.gpk_i8_configure(self._p(self._i8_ws), *self._i8_cfg), "gpk_i8_configure")
-            _I8_OWNER[dev] = me
-            self._i8_planes_ok = False
-        if need_planes and (self.i8_mode & 2) and not self._i8_planes_ok:
-            _lib.check(self.lib.gpk_i8_prepare_predict(self._p(self.Mlow_d), self.NP, self._stream()),
-                       "gpk_i8_prepare_predict")
-            self._i8_planes_ok = True
 
     def _chunk_rows_default(self) -> int:
         return int(min(16384, max(128, (2 << 30) // (self.NP * 8)))) // 128 * 128
@@ -120,6 +76,20 @@ class DeviceGP:
     def _p(t):
         return C.c_void_p(t.data_ptr())
 
+    def upload(self, X_host, y_host):
+        """Replace the resident training inputs / targets from host tensors of the same shape (pinned ones copy
+        asynchronously on the engine's stream).  Invalidates the factor held."""
+        t = self.torch
+        X_host = X_host if t.is_tensor(X_host) else t.from_numpy(np.ascontiguousarray(X_host, dtype=np.float64))
+        y_host = y_host if t.is_tensor(y_host) else t.from_numpy(np.ascontiguousarray(y_host, dtype=np.float64))
+        if tuple(X_host.shape) != (self.N, self.D) or tuple(y_host.reshape(self.N, -1).shape) != (self.N, self.T):
+            raise ValueError("upload: shapes must match the training set the engine was built for")
+        with t.cuda.device(self.device):
+            self.X_d.copy_(X_host, non_blocking=True)
+            self.y_d[: self.N].copy_(y_host.reshape(self.N, self.T), non_blocking=True)
+        self.factored = None
+        self.a_holds_L = False
+
     # -- log marginal likelihood (+ gradient) ------------------------------------------------
     def lml(self, inv_ls, c: float, noise: float, with_grad: bool):
         """Returns (lml, g_c, g_ls[D], g_noise); lml = -inf when K is not positive definite
@@ -127,8 +97,6 @@ class DeviceGP:
         t = self.torch
         self._bufs()
         with t.cuda.device(self.device):
-            self._i8_bind()
-            self._i8_planes_ok = False
             rc = self.lib.gpk_lml_eval(
                 self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter, self._p(self.y_d), self.T,
                 self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self._p(self.u_d), self._p(self.alpha_d),
@@ -154,8 +122,6 @@ class DeviceGP:
         key = (tuple(float(v) for v in inv_ls), float(c), float(noise))
         with t.cuda.device(self.device):
             st = self._stream()
-            self._i8_bind()
-            self._i8_planes_ok = False
             _lib.check(self.lib.gpk_gram(self._p(self.X_d), self.N, self.D, _lib.darr(inv_ls), c, noise, self.jitter,
                                          self._p(self.A_d), self.NP, 1, st), "gpk_gram")
             _lib.check(self.lib.gpk_potrf_inv(self._p(self.A_d), self._p(self.Mlow_d), self._p(self.Mup_d), self.NP,
@@ -163,8 +129,6 @@ class DeviceGP:
             _lib.check(self.lib.gpk_potrs(self._p(self.Mlow_d), self._p(self.Mup_d), self.NP, self._p(self.y_d),
                                           self._p(self.u_d), self._p(self.alpha_d), self.T, st), "gpk_potrs")
             info = int(self.info_d[:1].cpu()[0])
-            if info == 0:
-                self._i8_bind(need_planes=True)
         self.factored = key if info == 0 else None
         self.a_holds_L = info == 0
         return info
@@ -191,17 +155,22 @@ class DeviceGP:
             return K[: self.N, : self.N].cpu().numpy()
 
     # -- predict -------------------------------------------------------------------------------
-    def _predict_ws(self, MPmax: int):
+    def _predict_ws(self, MPmax: int, mean_only: bool = False):
         """Device scratch for query chunks of up to MPmax rows (gpk_predict carves it).  Small ones (the 1..128-row
         control-tick calls of simple_gp.py:187-201 / mpc.py:1490-1509) are kept between calls, so a predict is
-        ONE C-ABI call: H2D, four launches, D2H, one stream sync, no allocation on the way."""
-        ws = getattr(self, "_pws", None)
+        ONE C-ABI call: H2D, the launches, D2H, one stream sync, no allocation on the way.  mean_only: the fused
+        kernel's scratch (no M x N cross-Gram: MPmax*(D + T*(1 + splits)) doubles)."""
+        slot = "_pws_mean" if mean_only else "_pws"
+        ws = getattr(self, slot, None)
         if ws is not None and ws[0] >= MPmax:
             return ws
         t = self.torch
-        n = int(self.lib.gpk_predict_workspace_doubles(MPmax, self.NP, self.D, self.T))
+        if mean_only:
+            n = int(self.lib.gpk_predict_mean_workspace_doubles(MPmax, self.N, self.D, self.T))
+        else:
+            n = int(self.lib.gpk_predict_workspace_doubles(MPmax, self.NP, self.D, self.T))
         ws = (MPmax, t.empty(n, dtype=t.float64, device=self.device), n, np.zeros(1, dtype=np.int32))
-        self._pws = ws if n * 8 <= (256 << 20) else None
+        setattr(self, slot, ws if n * 8 <= (256 << 20) else None)
         return ws
 
     def _target_scale(self, y_mean, y_std):
@@ -223,8 +192,9 @@ class DeviceGP:
         Xq = np.ascontiguousarray(Xq, dtype=np.float64)
         M = Xq.shape[0]
         NP, T = self.NP, self.T
-        if chunk_rows is None:
-            chunk_rows = self._chunk_rows_default()
+        mean_only = not return_std and not return_cov
+        if chunk_rows is None:   # mean only: nothing M x N is stored, so the chunk is bounded by the staging copy alone
+            chunk_rows = 131072 if mean_only else self._chunk_rows_default()
         chunk_rows = max(128, (chunk_rows // 128) * 128)
         if return_cov:
             chunk_rows = ((M + 127) // 128) * 128
@@ -236,9 +206,8 @@ class DeviceGP:
             st = self._stream()
             ym, ys = self._target_scale(y_mean, y_std)
             inv_h = _lib.darr(inv_ls)
-            self._i8_bind(need_planes=True)
             if not return_cov:
-                MPmax, ws_d, ws_n, neg_h = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128))
+                MPmax, ws_d, ws_n, neg_h = self._predict_ws(min(chunk_rows, ((M + 127) // 128) * 128), mean_only)
                 for s in range(0, M, chunk_rows):
                     m = min(chunk_rows, M - s)
                     rc = self.lib.gpk_predict(
@@ -281,14 +250,14 @@ def predict_stacked(engines, Xqs, scales, return_std: bool):
 
     engines: DeviceGP list; Xqs: one (M, D_k) float64 array per engine; scales: (y_mean, y_std) per engine.
     Returns [(mean (M,T_k), std (M,T_k) | None, clamped-row count)] in order, or None when the batch does not qualify
-    (different devices, more rows than one chunk, more than MAX_STACKED models, int8 experiment on) -- the caller then
+    (different devices, more rows than one chunk, more than MAX_STACKED models) -- the caller then
     loops over DeviceGP.predict, the same kernels one model at a time."""
     K = len(engines)
     if K < 1 or K > _lib.MAX_STACKED or len({id(e) for e in engines}) != K:
         return None
     dev = engines[0].device
     M = int(Xqs[0].shape[0])
-    if M < 1 or any(e.device != dev or e.factored is None or getattr(e, "i8_mode", 0) for e in engines):
+    if M < 1 or any(e.device != dev or e.factored is None for e in engines):
         return None
     if any(x.shape[0] != M for x in Xqs) or any(M > e._chunk_rows_default() for e in engines):
         return None
@@ -303,7 +272,6 @@ def predict_stacked(engines, Xqs, scales, return_std: bool):
         with t.cuda.device(dev):
             st = engines[0]._stream()
             for k, (e, Xq, (y_mean, y_std)) in enumerate(zip(engines, Xqs, scales)):
-                e._i8_bind()
                 Xq = np.ascontiguousarray(Xq, dtype=np.float64)
                 if Xq.shape[1] != e.D:
                     raise ValueError(f"model {k}: query has {Xq.shape[1]} features, the training set {e.D}")
