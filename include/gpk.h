@@ -118,6 +118,18 @@ typedef struct GpkStackedModel {
 } GpkStackedModel;
 int gpk_predict_stacked(const GpkStackedModel* models_h, int n_models, int Mq, void* stream);
 
+/* evaluate_gp_offline.py:277-312 behind the batched predict: per-component and whole-row error sums of the nominal
+ * model (zero residual) and of the GP-corrected one, reduced on the device in a fixed order.
+ * Rtrue_d, Rpred_d: (M x C) row-major, C <= 8.  out_d (gpk_residual_metrics_out_len() = 46 doubles):
+ *   out[5j + 0..4] = sum t, sum t^2, sum (t-g)^2, #rows t^2 > (t-g)^2, sum (t - mean_j)^2        for component j < C
+ *   out[40 + 0..5] = sum se_nom, sum se_gp, #rows se_nom > se_gp, #rows se_nom < se_gp, sum acc_nom, sum acc_gp
+ *   (se = squared error summed over the components of a row, acc = components 3..5).
+ * ws_d: gpk_residual_metrics_workspace_doubles(M) doubles of scratch. */
+int gpk_residual_metrics_out_len(void);
+size_t gpk_residual_metrics_workspace_doubles(int M);
+int gpk_residual_metrics(const double* Rtrue_d, const double* Rpred_d, int M, int C, double* ws_d, double* out_d,
+                         void* stream);
+
 /* utilities */
 int gpk_extract_lower(const double* src_d, int NP, double* dst_d, int N, void* stream);
 int gpk_pad_copy(const double* src_d, int R, int C, double* dst_d, int RP, int CP, void* stream);

@@ -57,6 +57,19 @@ class OracleEngine:
         return m, s, None, 0
 
 
+    def predict_with_metrics(self, Xq, y_mean, y_std, R_true, chunk_rows=None):
+        """NumPy statement of gpk_residual_metrics' 46 sums (include/gpk.h) behind the mean-only predict"""
+        mean = self.predict(Xq, y_mean, y_std, False)[0]
+        t, e = R_true, R_true - mean
+        raw = np.zeros(46)
+        for j in range(t.shape[1]):
+            raw[5 * j: 5 * j + 5] = [t[:, j].sum(), (t[:, j] ** 2).sum(), (e[:, j] ** 2).sum(),
+                                     (t[:, j] ** 2 > e[:, j] ** 2).sum(), ((t[:, j] - t[:, j].mean()) ** 2).sum()]
+        sn, sg = (t ** 2).sum(1), (e ** 2).sum(1)
+        raw[40:46] = [sn.sum(), sg.sum(), (sn > sg).sum(), (sn < sg).sum(), (t[:, 3:6] ** 2).sum(), (e[:, 3:6] ** 2).sum()]
+        return mean, raw
+
+
 @pytest.fixture(autouse=True)
 def _oracle_engine(monkeypatch):
     monkeypatch.setattr(gpr_mod, "DeviceGP", OracleEngine)
@@ -404,3 +417,33 @@ def test_prior_covariance_matches_sklearn(n_targets):
     mg, cg = gpr_mod.GaussianProcessRegressor(kernel=k, n_targets=n_targets).predict(Xq, return_cov=True)
     assert mg.shape == ms.shape and cg.shape == cs.shape
     np.testing.assert_allclose(cg, cs, rtol=0, atol=1e-15)
+
+
+def test_evaluate_gp_from_device_side_sums_equals_the_host_route(tmp_path):
+    """offline.evaluate_gp takes the estimator's predict_with_residual_metrics (sums reduced behind the batched
+    predict) when the model has the reference's six components; the dict and the metrics table must equal what the
+    host route (the reference's own arithmetic, evaluate_gp_offline.py:225-312) computes from the same predictions."""
+    from unmanned_aerial_vehicles_b200 import offline
+    X, Y = _data(150, 10, 6, seed=9)
+    Y = 0.05 * Y
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        g = gpr_mod.GaussianProcessRegressor(kernel=RBF(0.5) + WhiteKernel(0.1), alpha=1e-4, normalize_y=True,
+                                             optimizer=None).fit(X, Y)
+    Xe = X + 0.05
+    Re = Y + 0.01 * np.random.default_rng(1).standard_normal(Y.shape)
+    fused = offline.evaluate_gp(g, Xe, Re, Xe[:, :6], Xe[:, 6:], save_prefix=tmp_path / "dev")
+
+    class HostOnly:                                   # same predictions, no fused hook -> the host route
+        def predict(self, Xq): return g.predict(Xq)
+    host = offline.evaluate_gp(HostOnly(), Xe, Re, Xe[:, :6], Xe[:, 6:], save_prefix=tmp_path / "host")
+    for blk in ("global", "acc_only", "fractions"):
+        for k, v in host[blk].items():
+            assert fused[blk][k] == pytest.approx(v, rel=1e-9, abs=1e-12), (blk, k)
+    assert list(fused["per_component"].columns) == list(host["per_component"].columns)
+    for col in host["per_component"].columns[1:]:
+        np.testing.assert_allclose(fused["per_component"][col], host["per_component"][col], rtol=1e-9, atol=1e-12)
+    assert (tmp_path / "dev_metrics.csv").read_text().splitlines()[0] == (tmp_path / "host_metrics.csv").read_text().splitlines()[0]
+    mean, sums = g.predict_with_residual_metrics(Xe, Re)
+    np.testing.assert_array_equal(mean, g.predict(Xe))
+    assert sums["n"] == 150 and len(sums["component"]) == 6 and len(sums["rows"]) == 6

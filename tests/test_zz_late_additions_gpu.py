@@ -97,3 +97,43 @@ def test_distributed_factor_predicts_like_the_single_gpu_engine(n, NB):
     np.testing.assert_allclose(mean, m_o, rtol=1e-6, atol=1e-9)
     assert np.max(np.abs(std - s_o)) <= 1e-8
     np.testing.assert_allclose(g.predict(Xq[:5]), m_o[:5], rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m", [1, 700, 5000])
+def test_residual_metrics_reduced_on_device_match_numpy(m):
+    """gpk_residual_metrics behind the fused mean-only predict (evaluate_gp_offline.py:277-312):
+    the 46 sums against NumPy on the same predictions, and the evaluate_gp dict built from them against the host
+    route."""
+    import warnings
+    from sklearn.gaussian_process.kernels import RBF, WhiteKernel
+    from unmanned_aerial_vehicles_b200 import GaussianProcessRegressor, offline
+    rng = np.random.default_rng(8)
+    X = rng.standard_normal((900, 10))
+    Y = 0.05 * np.sin(X @ rng.standard_normal((10, 6)) / 3) + 0.005 * rng.standard_normal((900, 6))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        g = GaussianProcessRegressor(kernel=RBF(0.8) + WhiteKernel(0.05), alpha=1e-4, normalize_y=True,
+                                     optimizer=None).fit(X, Y)
+    Xe = X[rng.integers(0, 900, m)] + 0.05 * rng.standard_normal((m, 10))
+    Re = 0.05 * np.sin(Xe @ rng.standard_normal((10, 6)) / 3)
+    mean, sums = g.predict_with_residual_metrics(Xe, Re)
+    want_mean = g.predict(Xe)
+    np.testing.assert_allclose(mean, want_mean, rtol=0, atol=1e-13)
+    e = Re - mean
+    for j in range(6):
+        t = Re[:, j]
+        want = [t.sum(), (t ** 2).sum(), (e[:, j] ** 2).sum(), float((t ** 2 > e[:, j] ** 2).sum()), ((t - t.mean()) ** 2).sum()]
+        np.testing.assert_allclose(sums["component"][j], want, rtol=1e-11, atol=1e-15)
+    sn, sg = (Re ** 2).sum(1), (e ** 2).sum(1)
+    want = [sn.sum(), sg.sum(), float((sn > sg).sum()), float((sn < sg).sum()), (Re[:, 3:] ** 2).sum(), (e[:, 3:] ** 2).sum()]
+    np.testing.assert_allclose(sums["rows"], want, rtol=1e-11, atol=1e-15)
+    if m > 1:
+        class HostOnly:
+            def predict(self, Xq): return g.predict(Xq)
+        dev = offline.evaluate_gp(g, Xe, Re, Xe[:, :6], Xe[:, 6:])
+        host = offline.evaluate_gp(HostOnly(), Xe, Re, Xe[:, :6], Xe[:, 6:])
+        for col in host["per_component"].columns[1:]:
+            np.testing.assert_allclose(dev["per_component"][col], host["per_component"][col], rtol=1e-8, atol=1e-12)
+        assert dev["global"]["mse_gp"] == pytest.approx(host["global"]["mse_gp"], rel=1e-9)
+        assert dev["fractions"] == pytest.approx(host["fractions"], abs=1e-12)

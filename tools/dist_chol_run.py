@@ -12,6 +12,7 @@ ap.add_argument("--size", dest="n", type=int, default=200000); ap.add_argument("
 ap.add_argument("--check", action="store_true")
 ap.add_argument("--grid", default="", help="PrxPc, e.g. 2x4 (default: most square)")
 ap.add_argument("--no-lookahead", action="store_true")
+ap.add_argument("--trace", action="store_true", help="CUDA-event spans per phase and panel (rank 0's and the slowest rank's summary)")
 ap.add_argument("--predict-rows", type=int, default=0, help="time DistGP.predict(return_std=True) on this many query rows")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
@@ -28,6 +29,9 @@ grid = tuple(int(v) for v in a.grid.split("x")) if a.grid else None
 g = DistGP(X, Y, jit, NB=a.nb, grid=grid, lookahead=not a.no_lookahead)
 torch.cuda.synchronize()
 if world > 1: dist.barrier()
+if a.trace:
+    g.ops.trace = []
+g.ops.bcast_bytes = g.ops.bcast_calls = 0
 t1 = time.perf_counter()
 info = g.factor(1.0 / ls, 1.0, noise)
 torch.cuda.synchronize()
@@ -44,6 +48,23 @@ out = {"what": "dist_chol", "n": a.n, "nb": a.nb, "n_gpus": world, "grid": f"{g.
        "assemble_factor_s": t2 - t1, "solve_lml_s": t3 - t2, "lml": lml, "potrf_alg_tflops": (a.n ** 3 / 3) / (t2 - t1) / 1e12,
        "executed_gemm_tflops": float(fl[0]) / (t2 - t1) / 1e12, "max_mem_gib_per_gpu": float(mem[0]),
        "local_gib": g.local_bytes() / 2 ** 30}
+out["bcast_GB_rank0"] = g.ops.bcast_bytes / 1e9
+out["bcast_calls_rank0"] = g.ops.bcast_calls
+if a.trace:
+    # per-phase seconds on this rank's streams: main = diag_potrf_inv, panel_gemm, update_*, wait_panel (stall for the
+    # next panel's broadcasts); side = bcast_panel_rows / bcast_panel_cols; bcast_diag_inverse sits on the main stream
+    summ = g.ops.trace_summary()
+    g.ops.trace = None
+    allr = [None] * world
+    if world > 1:
+        dist.all_gather_object(allr, summ)
+    else:
+        allr = [summ]
+    out["phases_rank0"] = {k: round(v["seconds"], 4) for k, v in sorted(allr[0].items())}
+    out["phases_max_over_ranks"] = {k: round(max(r.get(k, {"seconds": 0})["seconds"] for r in allr), 4) for k in sorted(allr[0])}
+    out["phases_min_over_ranks"] = {k: round(min(r.get(k, {"seconds": 0})["seconds"] for r in allr), 4) for k in sorted(allr[0])}
+    big = max(allr[0].get("bcast_panel_rows", {"seconds": 0})["seconds"], 1e-9)
+    out["bcast_panel_rows_GBps_rank0"] = out["bcast_GB_rank0"] / big if "bcast_panel_rows" in allr[0] else None
 if a.predict_rows > 0:                                  # collective: every rank runs it on the same rows
     Xq = X[np.random.default_rng(7).integers(0, a.n, a.predict_rows)] + 0.05
     g.predict(Xq[:256], return_std=True)                # warm-up

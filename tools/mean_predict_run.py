@@ -25,6 +25,7 @@ eng = DeviceGP(X, Y, 1e-6)
 assert eng.factor(np.ones(D), 1.0, 0.01) == 0
 rq = np.random.default_rng(7)
 Xq = (rq.standard_normal((M // 20, 1, D)) + 0.05 * np.cumsum(rq.standard_normal((M // 20, 20, D)), 1)).reshape(-1, D)
+M = Xq.shape[0]                                          # whole 20-step trajectories
 P = lambda t: C.c_void_p(t.data_ptr()); st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 inv = _lib.darr(np.ones(D))

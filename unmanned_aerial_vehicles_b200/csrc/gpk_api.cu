@@ -14,6 +14,9 @@ cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*,
                                     double*, cudaStream_t);
 cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
 int gpk_mean_fused_splits(int MP, int N);
+int gpk_metrics_blocks(int M);
+int gpk_metrics_rec();
+cudaError_t gpk_launch_residual_metrics(const double*, const double*, int, int, double*, double*, cudaStream_t);
 cudaError_t gpk_launch_predict_mean_fused(const double*, int, int, const double*, int, int, const GpkKernelParams&,
                                           const double*, int, const double*, const double*, double*, double*,
                                           cudaStream_t);
@@ -293,6 +296,16 @@ int gpk_predict_stacked(const GpkStackedModel* models_h, int n_models, int Mq, v
     if (rc) return rc;
   }
   GPK_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int gpk_residual_metrics_out_len(void) { return gpk_metrics_rec(); }
+size_t gpk_residual_metrics_workspace_doubles(int M) { return M < 1 ? 0 : (size_t)gpk_metrics_blocks(M) * gpk_metrics_rec(); }
+int gpk_residual_metrics(const double* Rtrue_d, const double* Rpred_d, int M, int C, double* ws_d, double* out_d,
+                         void* stream) {
+  if (!Rtrue_d) return -1; if (!Rpred_d) return -2; if (M < 1) return -3; if (C < 1 || C > 8) return -4;
+  if (!ws_d) return -5; if (!out_d) return -6;
+  GPK_CHECK(gpk_launch_residual_metrics(Rtrue_d, Rpred_d, M, C, ws_d, out_d, (cudaStream_t)stream));
   return 0;
 }
 

@@ -88,10 +88,14 @@ __global__ void __launch_bounds__(256, 2) gpk_cross_gram_kernel(const double* __
 //   W = sum_t alpha_t alpha_t^T - T * Kinv ;   acc[d]   = sum_ij W_ij Kc_ij (dx_d/l_d)^2   (d < D)
 //   acc[DP] = sum_ij W_ij Kc_ij  (d/dlog c),   acc[DP+1] = tr(W)  (d/dlog noise = 0.5*noise*tr W)
 // over the lower tiles (off-diagonal pairs counted twice).  partial[(block), DP+2].
+// General form: a (rows x cols) block of the matrix whose row / column entries carry the GLOBAL indices gi0 + r,
+// gj0 + c (the distributed factorisation calls it once per owned tile; the single-GPU path once for the whole matrix
+// with Xr == Xc, gi0 == gj0 == 0).  Only entries with global column <= global row are counted.
 template <int DP>
-__global__ void __launch_bounds__(256) gpk_grad_kernel(const double* __restrict__ X, int ldx, int N,
-                                                       GpkKernelParams p, const double* __restrict__ alpha, int lda,
-                                                       int T, const double* __restrict__ Kinv, int ldk,
+__global__ void __launch_bounds__(256) gpk_grad_kernel(const double* __restrict__ Xr, const double* __restrict__ Xc, int ldx,
+                                                       int nr, int nc, long long gi0, long long gj0, GpkKernelParams p,
+                                                       const double* __restrict__ ar, const double* __restrict__ ac,
+                                                       int lda, int T, const double* __restrict__ Kinv, int ldk,
                                                        double* __restrict__ partial, int accum) {
   const int tj = blockIdx.x, ti = blockIdx.y;
   const int bid = blockIdx.y * gridDim.x + blockIdx.x;
@@ -102,30 +106,32 @@ __global__ void __launch_bounds__(256) gpk_grad_kernel(const double* __restrict_
   double acc[DP + 2];
 #pragma unroll
   for (int d = 0; d < DP + 2; ++d) acc[d] = 0.0;
-  if (tj <= ti) {
-    load_scaled_rows<DP>(xi, X, ldx, i0, N, p, tid);
-    load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
+  if (gj0 + j0 <= gi0 + i0 + KTILE - 1) {
+    load_scaled_rows<DP>(xi, Xr, ldx, i0, nr, p, tid);
+    load_scaled_rows<DP>(xj, Xc, ldx, j0, nc, p, tid);
     for (int idx = tid; idx < KTILE * T; idx += 256) {
       int r = idx / T, t = idx % T;
-      ai[r][t] = (i0 + r < N) ? alpha[(size_t)(i0 + r) * lda + t] : 0.0;
-      aj[r][t] = (j0 + r < N) ? alpha[(size_t)(j0 + r) * lda + t] : 0.0;
+      ai[r][t] = (i0 + r < nr) ? ar[(size_t)(i0 + r) * lda + t] : 0.0;
+      aj[r][t] = (j0 + r < nc) ? ac[(size_t)(j0 + r) * lda + t] : 0.0;
     }
     __syncthreads();
     const int ty = tid >> 4, tx = tid & 15;
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
       const int li = ty * 4 + a, i = i0 + li;
+      const long long gi = gi0 + i;
       const double* kr = Kinv + (size_t)i * ldk + j0 + tx * 4;
       double2 k01 = *reinterpret_cast<const double2*>(kr), k23 = *reinterpret_cast<const double2*>(kr + 2);
       double kin[4] = {k01.x, k01.y, k23.x, k23.y};
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int lj = tx * 4 + b, j = j0 + lj;
-        if (i >= N || j > i) continue;
+        const long long gj = gj0 + j;
+        if (i >= nr || j >= nc || gj > gi) continue;
         double w = 0.0;
         for (int t = 0; t < T; ++t) w += ai[li][t] * aj[lj][t];
         w -= (double)T * kin[b];
-        if (i == j) { acc[DP] += w * p.c; acc[DP + 1] += w; continue; }
+        if (gi == gj) { acc[DP] += w * p.c; acc[DP + 1] += w; continue; }
         double sq[DP], d2 = 0.0;
 #pragma unroll
         for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; sq[d] = df * df; d2 += sq[d]; }
@@ -450,13 +456,38 @@ cudaError_t gpk_launch_lml_grad(const double* X, int N, int D, const GpkKernelPa
     dim3 grid(nt, nt);
     for (int t0 = 0; t0 < T; t0 += GRAD_TC) {
       const int tc = (T - t0 < GRAD_TC) ? (T - t0) : GRAD_TC;
-#define CALL(DPV) gpk_grad_kernel<DPV><<<grid, 256, 0, st>>>(X, D, N, p, alpha + t0, T, tc, Kinv, NP, ws, t0 > 0)
+#define CALL(DPV) gpk_grad_kernel<DPV><<<grid, 256, 0, st>>>(X, X, D, N, N, 0, 0, p, alpha + t0, alpha + t0, T, tc, Kinv, NP, ws, t0 > 0)
       DISPATCH_DP(D, CALL); GPK_LAUNCHED();
 #undef CALL
     }
   }
   gpk_lml_finalize_kernel<<<1 + T + (with_grad ? DP + 2 : 0), 256, 0, st>>>(ws, nblocks, DP + 2, D, N, T, L, lstep, y, T, alpha, T, p, with_grad, out); GPK_LAUNCHED();
   gpk_lml_combine_kernel<<<1, 1, 0, st>>>(N, T, out); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+
+// One (rows x cols) block with global offsets (distributed gradient): partial sums ACCUMULATE into
+// ws ((rows/64) * (cols/64) * (DP+2) doubles, zeroed by the caller before the first block) when accum != 0.
+cudaError_t gpk_launch_grad_block(const double* Xr, int nr, long long gi0, const double* Xc, int nc, long long gj0, int D,
+                                  const GpkKernelParams& p, const double* ar, const double* ac, int T, const double* Kinv,
+                                  int ldk, int rows, int cols, double* ws, int accum, cudaStream_t st) {
+  if (T > GRAD_TC || rows % KTILE || cols % KTILE) return cudaErrorInvalidValue;
+  dim3 grid(cols / KTILE, rows / KTILE);
+#define CALL(DPV) gpk_grad_kernel<DPV><<<grid, 256, 0, st>>>(Xr, Xc, D, nr, nc, gi0, gj0, p, ar, ac, T, T, Kinv, ldk, ws, accum)
+  DISPATCH_DP(D, CALL); GPK_LAUNCHED();
+#undef CALL
+  return cudaGetLastError();
+}
+// out[d] = sum over blocks of ws[b][d], d < DP+2, fixed order (one thread per quantity)
+__global__ void gpk_grad_sum_kernel(const double* __restrict__ ws, int nblocks, int DPp2, double* __restrict__ out) {
+  const int d = threadIdx.x;
+  if (d >= DPp2) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += ws[(size_t)b * DPp2 + d];
+  out[d] = s;
+}
+cudaError_t gpk_launch_grad_sum(const double* ws, int nblocks, int D, double* out, cudaStream_t st) {
+  gpk_grad_sum_kernel<<<1, 64, 0, st>>>(ws, nblocks, gpk_dp_of(D) + 2, out); GPK_LAUNCHED();
   return cudaGetLastError();
 }
 
@@ -602,5 +633,92 @@ cudaError_t gpk_launch_fix_diag(double* A, int lda, int n, int n_valid, double a
 }
 cudaError_t gpk_launch_logdiag(const double* A, int lda, int n, double* s, cudaStream_t st) {
   gpk_logdiag_kernel<<<1, 256, 0, st>>>(A, lda, n, s); GPK_LAUNCHED();
+  return cudaGetLastError();
+}
+
+// ---- residual metrics behind the batched predict (evaluate_gp_offline.py:277-312) -------------
+// For true residuals R (M x C) and GP-predicted residuals G (M x C), C <= 8, per component j:
+//   S[j][0] = sum t          S[j][1] = sum t^2 (nominal model = zero residual: its squared error)
+//   S[j][2] = sum (t - g)^2  S[j][3] = #rows with t^2 > (t - g)^2      S[j][4] = sum (t - mean_j)^2   (second pass)
+// and over whole rows (se = squared error summed over components; acc = components 3..5 when C >= 6):
+//   Gl[0] = sum se_nom, Gl[1] = sum se_gp, Gl[2] = #rows se_nom > se_gp, Gl[3] = #rows se_nom < se_gp,
+//   Gl[4] = sum acc_nom, Gl[5] = sum acc_gp.
+// HBM-bound: 16*C bytes per row, each read once per pass (the second pass re-reads R only).  Two stages, fixed order:
+// every CTA owns a contiguous row range and leaves one partial record; one CTA adds the records in order.
+#define MET_C 8
+#define MET_REC (MET_C * 5 + 6)
+__device__ __forceinline__ double met_block_sum(double v, double* sh) {
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  if (threadIdx.x == 0) for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += sh[w];
+  return s;   // valid in thread 0
+}
+__global__ void __launch_bounds__(256) gpk_metrics_pass1_kernel(const double* __restrict__ R, const double* __restrict__ G,
+                                                                int M, int Cc, int rows_per_block,
+                                                                double* __restrict__ partial) {
+  __shared__ double sh[8];
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  double st[MET_C], st2[MET_C], se2[MET_C], nb[MET_C], gl[6];
+#pragma unroll
+  for (int j = 0; j < MET_C; ++j) st[j] = st2[j] = se2[j] = nb[j] = 0.0;
+#pragma unroll
+  for (int q = 0; q < 6; ++q) gl[q] = 0.0;
+  for (int r = r0 + threadIdx.x; r < r1; r += 256) {
+    double sn = 0.0, sg = 0.0, an = 0.0, ag = 0.0;
+#pragma unroll
+    for (int j = 0; j < MET_C; ++j)
+      if (j < Cc) {
+        const double t = R[(size_t)r * Cc + j], e = t - G[(size_t)r * Cc + j], t2 = t * t, e2 = e * e;
+        st[j] += t; st2[j] += t2; se2[j] += e2; nb[j] += (t2 > e2) ? 1.0 : 0.0;
+        sn += t2; sg += e2;
+        if (j >= 3 && j < 6) { an += t2; ag += e2; }
+      }
+    gl[0] += sn; gl[1] += sg; gl[2] += (sn > sg) ? 1.0 : 0.0; gl[3] += (sn < sg) ? 1.0 : 0.0; gl[4] += an; gl[5] += ag;
+  }
+  double* rec = partial + (size_t)blockIdx.x * MET_REC;
+#pragma unroll
+  for (int j = 0; j < MET_C; ++j) {
+    double a = met_block_sum(st[j], sh), b = met_block_sum(st2[j], sh), c = met_block_sum(se2[j], sh), d = met_block_sum(nb[j], sh);
+    if (threadIdx.x == 0) { rec[j * 5 + 0] = a; rec[j * 5 + 1] = b; rec[j * 5 + 2] = c; rec[j * 5 + 3] = d; rec[j * 5 + 4] = 0.0; }
+  }
+#pragma unroll
+  for (int q = 0; q < 6; ++q) { double a = met_block_sum(gl[q], sh); if (threadIdx.x == 0) rec[MET_C * 5 + q] = a; }
+}
+__global__ void __launch_bounds__(256) gpk_metrics_pass2_kernel(const double* __restrict__ R, int M, int Cc, int rows_per_block,
+                                                                const double* __restrict__ out, double* __restrict__ partial) {
+  __shared__ double sh[8];
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  double dv[MET_C], mu[MET_C];
+#pragma unroll
+  for (int j = 0; j < MET_C; ++j) { dv[j] = 0.0; mu[j] = (j < Cc) ? out[j * 5 + 0] / (double)M : 0.0; }
+  for (int r = r0 + threadIdx.x; r < r1; r += 256)
+#pragma unroll
+    for (int j = 0; j < MET_C; ++j)
+      if (j < Cc) { const double d = R[(size_t)r * Cc + j] - mu[j]; dv[j] += d * d; }
+#pragma unroll
+  for (int j = 0; j < MET_C; ++j) { double a = met_block_sum(dv[j], sh); if (threadIdx.x == 0) partial[(size_t)blockIdx.x * MET_REC + j * 5 + 4] = a; }
+}
+// out[q] = sum over blocks of partial[b][q] for q in [q0, q1) with (q % 5 == 4) == second_pass among the component slots
+__global__ void gpk_metrics_reduce_kernel(const double* __restrict__ partial, int nblocks, int second_pass, double* __restrict__ out) {
+  const int q = threadIdx.x;
+  if (q >= MET_REC) return;
+  const bool comp = q < MET_C * 5, dev = comp && (q % 5 == 4);
+  if (second_pass ? !dev : dev) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * MET_REC + q];
+  out[q] = s;
+}
+int gpk_metrics_blocks(int M) { int b = (M + 1023) / 1024; return b < 1 ? 1 : (b > 592 ? 592 : b); }
+int gpk_metrics_rec() { return MET_REC; }
+cudaError_t gpk_launch_residual_metrics(const double* R, const double* G, int M, int Cc, double* partial, double* out,
+                                        cudaStream_t st) {
+  const int nb = gpk_metrics_blocks(M), rpb = (M + nb - 1) / nb;
+  gpk_metrics_pass1_kernel<<<nb, 256, 0, st>>>(R, G, M, Cc, rpb, partial); GPK_LAUNCHED();
+  gpk_metrics_reduce_kernel<<<1, 64, 0, st>>>(partial, nb, 0, out); GPK_LAUNCHED();
+  gpk_metrics_pass2_kernel<<<nb, 256, 0, st>>>(R, M, Cc, rpb, out, partial); GPK_LAUNCHED();
+  gpk_metrics_reduce_kernel<<<1, 64, 0, st>>>(partial, nb, 1, out); GPK_LAUNCHED();
   return cudaGetLastError();
 }

@@ -243,6 +243,45 @@ class DeviceGP:
         return mean, std, cov, neg_total
 
 
+    def predict_with_metrics(self, Xq: np.ndarray, y_mean, y_std, R_true: np.ndarray, chunk_rows: int = 131072):
+        """Mean-only predict over all of Xq with the residual-metric reductions of evaluate_gp_offline.py:277-312 run
+        behind it ON THE DEVICE: the predicted residuals never leave HBM between the fused mean kernel and the
+        reductions; the host receives the (M, T) mean and gpk_residual_metrics' 46 sums (see include/gpk.h)."""
+        assert self.factored is not None, "factor() first"
+        t = self.torch
+        inv_ls, c, _ = self.factored
+        Xq = np.ascontiguousarray(Xq, dtype=np.float64)
+        R_true = np.ascontiguousarray(R_true, dtype=np.float64)
+        M, T = Xq.shape[0], self.T
+        if R_true.shape != (M, T):
+            raise ValueError(f"R_true must be {(M, T)}, got {R_true.shape}")
+        if T > 8:
+            raise ValueError("device-side residual metrics handle at most 8 components")
+        chunk_rows = max(128, (int(chunk_rows) // 128) * 128)
+        with self._plock, t.cuda.device(self.device):
+            st = self._stream()
+            ym, ys = self._target_scale(y_mean, y_std)
+            inv_h = _lib.darr(inv_ls)
+            MPc = min(chunk_rows, ((M + 127) // 128) * 128)
+            nws = int(self.lib.gpk_predict_mean_workspace_doubles(MPc, self.N, self.D, T))
+            ws = t.empty(nws, dtype=t.float64, device=self.device)
+            xq_d = t.as_tensor(Xq, device=self.device)
+            rt_d = t.as_tensor(R_true, device=self.device)
+            mean_d = t.empty((M + MPc, T), dtype=t.float64, device=self.device)
+            for s in range(0, M, chunk_rows):
+                m = min(chunk_rows, M - s)
+                MP = ((m + 127) // 128) * 128
+                _lib.check(self.lib.gpk_predict_mean_fused(self._p(xq_d[s:]), m, MP, self._p(self.X_d), self.N, self.D,
+                                                           inv_h, c, self._p(self.alpha_d), T, self._p(ym), self._p(ys),
+                                                           self._p(ws), self._p(mean_d[s:]), st), "gpk_predict_mean_fused")
+            nout = int(self.lib.gpk_residual_metrics_out_len())
+            mws = t.empty(int(self.lib.gpk_residual_metrics_workspace_doubles(M)), dtype=t.float64, device=self.device)
+            out_d = t.zeros(nout, dtype=t.float64, device=self.device)
+            _lib.check(self.lib.gpk_residual_metrics(self._p(rt_d), self._p(mean_d), M, T, self._p(mws), self._p(out_d),
+                                                     st), "gpk_residual_metrics")
+            return mean_d[:M].cpu().numpy(), out_d.cpu().numpy()
+
+
 def predict_stacked(engines, Xqs, scales, return_std: bool):
     """Several factored engines on ONE device answer the same number of query rows each in ONE C-ABI call
     (gpk_predict_stacked: one stream sync for all of them) -- the per-output members of the reference's schema B / C

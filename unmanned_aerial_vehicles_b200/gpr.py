@@ -238,6 +238,27 @@ class GaussianProcessRegressor(MultiOutputMixin, RegressorMixin, BaseEstimator):
             return y_mean, y_cov
         return self._shape_outputs(mean, std, nneg, return_std)
 
+    def predict_with_residual_metrics(self, X, R_true):
+        """``predict(X)`` plus the error sums evaluate_gp_offline.py:277-312 takes of it against the true residuals
+        ``R_true`` (same shape as the prediction), reduced on the device behind the batched predict.
+        Returns (mean as predict would, sums): sums["component"][j] = (sum t, sum t^2, sum (t-g)^2, #rows where the
+        GP's squared error is the smaller, sum (t - mean_j)^2); sums["rows"] = (sum se_nom, sum se_gp, #rows better,
+        #rows worse, sum acc_nom, sum acc_gp); sums["n"] = rows."""
+        X = check_array(X, ensure_2d=True, dtype="numeric")
+        if not hasattr(self, "X_train_"):
+            raise AttributeError("predict_with_residual_metrics needs a fitted model")
+        if X.shape[1] != self.X_train_.shape[1]:
+            raise ValueError(f"X has {X.shape[1]} features, but GaussianProcessRegressor is expecting "
+                             f"{self.X_train_.shape[1]} features as input.")
+        self._ensure_factored()
+        eng = self._engine
+        R_true = np.asarray(R_true, dtype=np.float64).reshape(X.shape[0], -1)
+        mean, raw = eng.predict_with_metrics(np.asarray(X, dtype=np.float64), self._yscale_b[0], self._yscale_b[1], R_true)
+        T = eng.T
+        sums = {"n": int(X.shape[0]), "component": [tuple(float(v) for v in raw[5 * j: 5 * j + 5]) for j in range(T)],
+                "rows": tuple(float(v) for v in raw[40:46])}
+        return self._shape_outputs(mean, None, 0, False), sums
+
     def _shape_outputs(self, mean, std, nneg, return_std):
         """sklearn's output shapes (_gpr.py:453-454, :497-498) and the clamped-variance warning (:485-491)"""
         y_mean = mean[:, 0] if (self.y_train_.ndim == 1 or mean.shape[1] == 1) else mean
