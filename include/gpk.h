@@ -56,6 +56,22 @@ int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double
                  const double* L_d, const double* y_d, const double* alpha_d, int T, const double* Kinv_d, int NP,
                  int with_grad, double* ws_d, double* out_d, void* stream);
 
+/* The gradient contraction of gpk_lml_grad on ONE (rows x cols) block of the matrix (the distributed gradient calls
+ * it once per owned tile of K^-1; dist_grad.py).  Row r of the block is training row gi0 + r (inputs Xr_d, nr valid
+ * rows, alpha_r_d), column c is training row gj0 + c (Xc_d, nc valid, alpha_c_d); only entries with global column <=
+ * global row are counted, strictly lower ones twice.  Kinv_d: the block of K^-1 (rows x cols, leading dimension
+ * ldk).  Per-64x64-tile partial sums go to ws_d (gpk_grad_block_workspace_doubles(rows, cols, D) doubles; added to
+ * what is there when accumulate != 0).  gpk_grad_block_sum adds the tiles in a fixed order:
+ * out_d[0..DP) = sum_ij W_ij K_ij ((x_id - x_jd) / l_d)^2 per feature (DP = gpk_grad_padded_dim(D) >= D),
+ * out_d[DP] = sum W_ij K_ij, out_d[DP+1] = tr W; the gradient w.r.t. the log-parameters is 1/2 of these (x noise for
+ * the trace), _gpr.py:629-651 + kernels.py:1577-1584.  T <= 8. */
+size_t gpk_grad_block_workspace_doubles(int rows, int cols, int D);
+int gpk_grad_padded_dim(int D);
+int gpk_grad_block(const double* Xr_d, int nr, long long gi0, const double* Xc_d, int nc, long long gj0, int D,
+                   const double* inv_ls_h, double c, const double* alpha_r_d, const double* alpha_c_d, int T,
+                   const double* Kinv_d, int ldk, int rows, int cols, double* ws_d, int accumulate, void* stream);
+int gpk_grad_block_sum(const double* ws_d, int rows, int cols, int D, double* out_d, void* stream);
+
 /* one whole log_marginal_likelihood(theta, eval_gradient) evaluation (_gpr.py:541-656):
  * gram -> potrf_inv -> potrs -> [lauum -> gradient] -> finalize.  A_d, Mlow_d, Mup_d are NP x NP scratch
  * (A_d ends as K^-1 lower tiles when with_grad, else with L's diagonal 128-blocks only: an objective evaluation
@@ -141,7 +157,10 @@ int gpk_gemm_nt(const double* A_d, int lda, const double* B_d, int ldb, double* 
 /* register-resident DMMA loop for the FP64 tensor peak; returns flops executed in *flops_h */
 int gpk_dmma_probe(int blocks, int iters, double* sink_d, double* flops_h, void* stream);
 
-/* building blocks of the distributed factorisation (dist_chol.py) */
+/* building blocks of the distributed factorisation (dist_chol.py).  There is NO entry point that
+ * takes a communicator: the 2-D block-cyclic driver is host-side panel scheduling (dist_chol.py / dist_grad.py) over
+ * torch.distributed's NCCL sub-communicators, calling gpk_cross_gram / gpk_potrf_inv / gpk_gemm_nt / gpk_grad_block
+ * and the helpers below per tile; a non-Python host would drive the same calls with its own ncclBroadcast. */
 /* transpose == 0: out (M x T) = beta*out + alpha * A (M x K) v (K x T);  != 0: out (K x T) += alpha * A^T v (M x T) */
 int gpk_gemv(const double* A_d, int lda, int M, int K, const double* v_d, int T, double* out_d, double alpha, double beta,
              int transpose, void* stream);

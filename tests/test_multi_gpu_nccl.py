@@ -85,7 +85,7 @@ def _worker(rank, world, port, q):
     Xd, Yd = _data(3000, 9, 3, seed=2)
     inv_ls, noise = 1.0 / np.linspace(0.8, 2.0, 9), 0.02
     eng = DeviceGP(Xd, Yd, 1e-6)
-    ref_lml, *_ = eng.lml(inv_ls, 1.0, noise, False)
+    ref_lml, _, gls_ref, gn_ref = eng.lml(inv_ls, 1.0, noise, True)
     assert eng.factor(inv_ls, 1.0, noise) == 0
     a_ref = eng.alpha_host()
     Xq9 = np.random.default_rng(6).standard_normal((300, 9))
@@ -97,11 +97,14 @@ def _worker(rank, world, port, q):
         gp.solve()
         lml = gp.lml()
         md, sd = gp.predict(Xq9, return_std=True)
+        lml_g, g_c, g_ls, g_noise = gp.lml_grad(inv_ls, 1.0, noise)         # distributed TRTRI + LAUUM + gradient
         phases = gp.ops.trace_summary()
         out[f"dist_{grid[0]}x{grid[1]}"] = {
             "lml_rel": abs(lml - ref_lml) / abs(ref_lml), "alpha_err": float(np.abs(gp.alpha_host() - a_ref).max()),
             "mean_err": float(np.abs(md - mr).max()), "std_err": float(np.abs(sd - sr).max()),
-            "bcast_bytes": int(gp.ops.bcast_bytes), "phases": sorted(phases)}
+            "bcast_bytes": int(gp.ops.bcast_bytes), "phases": sorted(phases),
+            "grad_err": float(max(np.max(np.abs(g_ls - gls_ref)) / np.max(np.abs(gls_ref)), abs(g_noise - gn_ref) / abs(gn_ref),
+                                  abs(lml_g - ref_lml) / abs(ref_lml)))}
     q.put((rank, out))
     dist.barrier()
     dist.destroy_process_group()
@@ -127,4 +130,5 @@ def test_sharded_paths_over_nccl_on_two_gpus():
             d = o[g]
             assert d["lml_rel"] < 1e-11 and d["alpha_err"] < 1e-8 and d["mean_err"] < 1e-9 and d["std_err"] < 1e-8, d
             assert d["bcast_bytes"] > 0 and "update_trailing" in d["phases"] and "diag_potrf_inv" in d["phases"], d
+            assert d["grad_err"] < 1e-7 and "lauum_update" in d["phases"] and "trtri_update" in d["phases"], d
     assert outs[0]["evals_here"] + outs[1]["evals_here"] > 10

@@ -13,6 +13,7 @@ ap.add_argument("--check", action="store_true")
 ap.add_argument("--grid", default="", help="PrxPc, e.g. 2x4 (default: most square)")
 ap.add_argument("--no-lookahead", action="store_true")
 ap.add_argument("--trace", action="store_true", help="CUDA-event spans per phase and panel (rank 0's and the slowest rank's summary)")
+ap.add_argument("--grad", action="store_true", help="also the distributed inverse (TRTRI + LAUUM) and the LML gradient: one full objective evaluation")
 ap.add_argument("--predict-rows", type=int, default=0, help="time DistGP.predict(return_std=True) on this many query rows")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
@@ -62,9 +63,44 @@ if a.trace:
         allr = [summ]
     out["phases_rank0"] = {k: round(v["seconds"], 4) for k, v in sorted(allr[0].items())}
     out["phases_max_over_ranks"] = {k: round(max(r.get(k, {"seconds": 0})["seconds"] for r in allr), 4) for k in sorted(allr[0])}
+    out["idle_before_phase_rank0"] = {k: round(v["idle_before_s"], 4) for k, v in sorted(allr[0].items()) if v["idle_before_s"] > 0}
+    out["idle_before_phase_max_over_ranks"] = {k: round(max(r.get(k, {"idle_before_s": 0})["idle_before_s"] for r in allr), 4)
+                                               for k in sorted(allr[0])}
     out["phases_min_over_ranks"] = {k: round(min(r.get(k, {"seconds": 0})["seconds"] for r in allr), 4) for k in sorted(allr[0])}
     big = max(allr[0].get("bcast_panel_rows", {"seconds": 0})["seconds"], 1e-9)
     out["bcast_panel_rows_GBps_rank0"] = out["bcast_GB_rank0"] / big if "bcast_panel_rows" in allr[0] else None
+if a.grad:
+    if a.trace:
+        g.ops.trace = []
+    b0 = g.ops.bcast_bytes
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    tg = time.perf_counter()
+    g.inverse()
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    t_inv = time.perf_counter() - tg
+    tg = time.perf_counter()
+    g_c, g_ls, g_noise = g.gradient()
+    torch.cuda.synchronize()
+    t_grad = time.perf_counter() - tg
+    memg = torch.tensor([torch.cuda.max_memory_allocated() / 2 ** 30], dtype=torch.float64, device="cuda")
+    if world > 1: dist.all_reduce(memg, op=dist.ReduceOp.MAX)
+    out.update({"inverse_trtri_lauum_s": t_inv, "inverse_alg_tflops_on_2N3_over_3": (2 * a.n ** 3 / 3) / t_inv / 1e12,
+                "gradient_contraction_s": t_grad, "objective_evaluation_with_gradient_s": (t2 - t1) + (t3 - t2) + t_inv + t_grad,
+                "grad_ls": [float(v) for v in g_ls], "grad_noise": float(g_noise), "grad_c": float(g_c),
+                "inverse_bcast_GB_rank0": (g.ops.bcast_bytes - b0) / 1e9, "max_mem_gib_per_gpu_with_inverse": float(memg[0])})
+    if a.trace:
+        summ = g.ops.trace_summary(); g.ops.trace = None
+        out["inverse_phases_rank0"] = {k: round(v["seconds"], 4) for k, v in sorted(summ.items())}
+        out["inverse_idle_before_phase_rank0"] = {k: round(v["idle_before_s"], 4) for k, v in sorted(summ.items()) if v["idle_before_s"] > 0}
+    if a.check and rank == 0:
+        from unmanned_aerial_vehicles_b200.engine import DeviceGP
+        e3 = DeviceGP(X, Y, jit)
+        _, gc_e, gls_e, gn_e = e3.lml(1.0 / ls, 1.0, noise, True)
+        out["check_grad_ls_maxrel"] = float(np.max(np.abs(g_ls - gls_e)) / np.max(np.abs(gls_e)))
+        out["check_grad_noise_rel"] = abs(g_noise - gn_e) / abs(gn_e)
+        del e3
 if a.predict_rows > 0:                                  # collective: every rank runs it on the same rows
     Xq = X[np.random.default_rng(7).integers(0, a.n, a.predict_rows)] + 0.05
     g.predict(Xq[:256], return_std=True)                # warm-up

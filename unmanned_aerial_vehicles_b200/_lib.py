@@ -17,6 +17,7 @@ SYMBOLS = (
     "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
     "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict_mean_workspace_doubles", "gpk_predict_mean_fused", "gpk_predict", "gpk_predict_stacked", "gpk_residual_metrics_out_len", "gpk_residual_metrics_workspace_doubles", "gpk_residual_metrics", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
     "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_leaf_phase_cycles", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
+    "gpk_grad_block_workspace_doubles", "gpk_grad_padded_dim", "gpk_grad_block", "gpk_grad_block_sum",
 )
 
 
@@ -78,6 +79,12 @@ def _declare(lib):
     lib.gpk_trimv.argtypes = [_p, _i, _p, _p, _i, _i, _p]
     lib.gpk_fix_diag.argtypes = [_p, _i, _i, _i, _d, _d, _p]
     lib.gpk_logdiag.argtypes = [_p, _i, _i, _p, _p]
+    lib.gpk_grad_block_workspace_doubles.argtypes = [_i, _i, _i]
+    lib.gpk_grad_block_workspace_doubles.restype = C.c_size_t
+    lib.gpk_grad_padded_dim.argtypes = [_i]
+    lib.gpk_grad_block.argtypes = [_p, _i, C.c_longlong, _p, _i, C.c_longlong, _i, _dp, _d, _p, _p, _i, _p, _i, _i, _i,
+                                   _p, _i, _p]
+    lib.gpk_grad_block_sum.argtypes = [_p, _i, _i, _i, _p, _p]
     lib.gpk_leaf_phase_cycles.argtypes = [_p]
     lib.gpk_launch_count.restype = C.c_ulonglong
     lib.gpk_profile_launch.argtypes = [_i, _dp, _dp, C.POINTER(C.c_int)]
@@ -85,7 +92,8 @@ def _declare(lib):
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("gpk_grad_workspace_doubles", "gpk_predict_workspace_doubles", "gpk_predict_mean_workspace_doubles",
-                        "gpk_residual_metrics_workspace_doubles", "gpk_launch_count"):
+                        "gpk_residual_metrics_workspace_doubles", "gpk_grad_block_workspace_doubles",
+                        "gpk_launch_count"):
             fn.restype = _i
 
 

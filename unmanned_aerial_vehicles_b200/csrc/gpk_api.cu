@@ -15,6 +15,10 @@ cudaError_t gpk_launch_predict_mean(const double*, int, int, int, const double*,
 cudaError_t gpk_launch_predict_std(const double*, int, int, double, const double*, int, double*, int*, cudaStream_t);
 int gpk_mean_fused_splits(int MP, int N);
 int gpk_metrics_blocks(int M);
+cudaError_t gpk_launch_grad_block(const double*, int, long long, const double*, int, long long, int, const GpkKernelParams&,
+                                  const double*, const double*, int, const double*, int, int, int, double*, int,
+                                  cudaStream_t);
+cudaError_t gpk_launch_grad_sum(const double*, int, int, double*, cudaStream_t);
 int gpk_metrics_rec();
 cudaError_t gpk_launch_residual_metrics(const double*, const double*, int, int, double*, double*, cudaStream_t);
 cudaError_t gpk_launch_predict_mean_fused(const double*, int, int, const double*, int, int, const GpkKernelParams&,
@@ -107,6 +111,29 @@ int gpk_lml_grad(const double* X_d, int N, int D, const double* inv_ls_h, double
                                 (cudaStream_t)stream));
   return 0;
 }
+
+size_t gpk_grad_block_workspace_doubles(int rows, int cols, int D) {
+  if (rows < 1 || cols < 1 || rows % 64 || cols % 64) return 0;
+  return (size_t)(rows / 64) * (cols / 64) * (size_t)(gpk_dp_of(D) + 2);
+}
+int gpk_grad_block(const double* Xr_d, int nr, long long gi0, const double* Xc_d, int nc, long long gj0, int D,
+                   const double* inv_ls_h, double c, const double* alpha_r_d, const double* alpha_c_d, int T,
+                   const double* Kinv_d, int ldk, int rows, int cols, double* ws_d, int accumulate, void* stream) {
+  GpkKernelParams p;
+  if (!Xr_d) return -1; if (nr < 0 || nr > rows) return -2; if (!Xc_d) return -4; if (nc < 0 || nc > cols) return -5;
+  if (make_params(p, D, inv_ls_h, c, 0.0, 0.0)) return -7;
+  if (!alpha_r_d) return -10; if (!alpha_c_d) return -11; if (T < 1 || T > 8) return -12;
+  if (!Kinv_d) return -13; if (ldk < cols) return -14; if (rows % 64 || cols % 64) return -15; if (!ws_d) return -17;
+  GPK_CHECK(gpk_launch_grad_block(Xr_d, nr, gi0, Xc_d, nc, gj0, D, p, alpha_r_d, alpha_c_d, T, Kinv_d, ldk, rows, cols,
+                                  ws_d, accumulate, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_grad_block_sum(const double* ws_d, int rows, int cols, int D, double* out_d, void* stream) {
+  if (!ws_d) return -1; if (rows % 64 || cols % 64) return -2; if (D < 1 || D > GPK_MAXD) return -4; if (!out_d) return -5;
+  GPK_CHECK(gpk_launch_grad_sum(ws_d, (rows / 64) * (cols / 64), D, out_d, (cudaStream_t)stream));
+  return 0;
+}
+int gpk_grad_padded_dim(int D) { return gpk_dp_of(D); }
 
 int gpk_lml_eval(const double* X_d, int N, int D, const double* inv_ls_h, double c, double noise, double jitter,
                  const double* y_d, int T, double* A_d, double* Mlow_d, double* Mup_d, double* u_d, double* alpha_d,

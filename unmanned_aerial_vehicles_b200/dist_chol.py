@@ -32,6 +32,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
+from .dist_grad import DistGradMixin
 
 
 def default_grid(P):
@@ -86,6 +87,12 @@ class CudaOps:
                 g = self.dist.new_group([r * Pc + c for r in range(Pr)]) if Pr > 1 else None
                 if c == pc:
                     self.groups["col"] = g
+            # NCCL builds a communicator at its first collective: do that here, not inside the first timed panel
+            one = self.t.zeros(1, dtype=self.t.float64, device=self.dev)
+            for kind in ("row", "col"):
+                if self.groups[kind] is not None:
+                    self.dist.all_reduce(one, group=self.groups[kind])
+            self.t.cuda.synchronize()
         self.grid = (Pr, Pc)
         return pr, pc
 
@@ -142,6 +149,24 @@ class CudaOps:
     def logdiag(self, A, n, acc):
         _lib.check(self.lib.gpk_logdiag(self._p(A), A.stride(0), n, self._p(acc), self._st()), "gpk_logdiag")
 
+    # -- gradient from the distributed inverse (dist_grad.py) ------------------------------------------
+    def grad_ws(self, NB, D):
+        n = int(self.lib.gpk_grad_block_workspace_doubles(NB, NB, D))
+        return self.t.zeros(n, dtype=self.t.float64, device=self.dev)
+
+    def grad_block(self, Xr, nr, gi0, Xc, nc, gj0, D, inv_ls, c, ar, ac, T, Kinv, rows, cols, ws, accum):
+        _lib.check(self.lib.gpk_grad_block(self._p(Xr), nr, gi0, self._p(Xc), nc, gj0, D, _lib.darr(inv_ls), c,
+                                           self._p(ar), self._p(ac), T, self._p(Kinv), Kinv.stride(0), rows, cols,
+                                           self._p(ws), int(accum), self._st()), "gpk_grad_block")
+
+    def grad_sum(self, ws, NB, D, empty):
+        """(D + 2, 1) device tensor: per-feature sums, sum W K, tr W (the padded feature slots dropped)"""
+        DP = int(self.lib.gpk_grad_padded_dim(D))
+        out = self.t.zeros(DP + 2, dtype=self.t.float64, device=self.dev)
+        if not empty:
+            _lib.check(self.lib.gpk_grad_block_sum(self._p(ws), NB, NB, D, self._p(out), self._st()), "gpk_grad_block_sum")
+        return self.t.cat([out[:D], out[DP:]]).reshape(-1, 1).contiguous()
+
     def _multi(self):
         return self.dist.is_initialized() and self.rank_world()[1] > 1
 
@@ -169,16 +194,23 @@ class CudaOps:
             yield
         finally:
             e1.record(st)
-            self.trace.append((phase, k, e0, e1))
+            self.trace.append((phase, k, e0, e1, st.cuda_stream == self.side_stream.cuda_stream))
 
     def trace_summary(self):
-        """seconds per phase (summed over panels) from the recorded spans; synchronises"""
+        """seconds per phase (summed over panels) from the recorded spans, and -- for the spans of the main stream, in
+        issue order -- the idle time in FRONT of each phase ("idle_before_s": the stream had nothing to run, i.e. the
+        host had not issued it yet or an earlier wait had not been satisfied); synchronises"""
         self.t.cuda.synchronize()
         out = {}
-        for phase, k, e0, e1 in self.trace or []:
-            d = out.setdefault(phase, {"seconds": 0.0, "spans": 0, "max_ms": 0.0})
+        prev_end = None
+        for phase, k, e0, e1, on_side in self.trace or []:
+            d = out.setdefault(phase, {"seconds": 0.0, "spans": 0, "max_ms": 0.0, "idle_before_s": 0.0})
             ms = e0.elapsed_time(e1)
             d["seconds"] += ms * 1e-3; d["spans"] += 1; d["max_ms"] = max(d["max_ms"], ms)
+            if not on_side:
+                if prev_end is not None:
+                    d["idle_before_s"] += max(0.0, prev_end.elapsed_time(e0)) * 1e-3
+                prev_end = e1
         return out
 
     def allreduce_sum(self, buf):
@@ -207,8 +239,9 @@ class CudaOps:
         return v
 
 
-class DistGP:
-    """Distributed exact GP: factor K(theta) + alpha*I, solve for alpha_, evaluate the LML."""
+class DistGP(DistGradMixin):
+    """Distributed exact GP: factor K(theta) + alpha*I, solve for alpha_, evaluate the LML; its gradient through the
+    distributed inverse (dist_grad.py: inverse(), gradient(), lml_grad())."""
 
     def __init__(self, X, y2d, jitter, NB=2048, ops=None, grid=None, lookahead=True):
         self.ops = ops if ops is not None else CudaOps()
@@ -259,6 +292,7 @@ class DistGP:
         o.info_slots(nb)
         self.gemm_flops = 0.0
         self.factored = False
+        self.mt = self.kinv = None        # dist_grad.py allocates them on the first inverse()
 
     def _span(self, phase, k=-1):
         sp = getattr(self.ops, "span", None)
