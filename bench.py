@@ -12,8 +12,9 @@ every N (each under its own guard: a failure is recorded in place, the headline 
                   at N > 1 the runs are claimed from a shared queue (parallel.fit_sharded_restarts): strong scaling
   predict_sharded config 3 shape, 81 920 x N query rows through parallel.predict_sharded, gather inside the timed
                   region (all_gather_into_tensor over NCCL); mean+std and mean-only
-  dist_chol       config 5 path, DistGP.factor + solve + lml (2-D block-cyclic Cholesky, NCCL panel broadcasts) at
-                  N_train = 20k / 100k / 140k / 200k for 1 / 2 / 4 / 8 GPUs, checked against the single-GPU engine
+  dist_chol       config 5 path, DistGP.factor + solve + lml (2-D block-cyclic Cholesky, NCCL panel broadcasts) and
+                  the gradient from the distributed inverse, at N_train = 20k / 100k / 140k / 200k for 1 / 2 / 4 / 8
+                  GPUs, checked against the single-GPU engine at 20k
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--skip full_fit,predict_sharded,...]
 """
@@ -383,10 +384,26 @@ def extra_dist_chol(ctx, est, peak):
                "frac_fp64_peak_per_gpu": fl / t_f / 1e12 / ctx.world / peak,
                "bcast_GB_this_rank": ops.bcast_bytes / 1e9, "bcast_calls_this_rank": ops.bcast_calls,
                "local_GB": gp.local_bytes() / 1e9}
+        # the gradient at this size: distributed TRTRI + LAUUM (2 N^3 / 3) and the tile-wise contraction (dist_grad.py)
+        ctx.barrier()
+        b0 = ops.bcast_bytes
+        t0 = time.perf_counter()
+        gp.inverse()
+        g_c, g_ls, g_noise = gp.gradient()
+        torch.cuda.synchronize()
+        t_g = ctx.max_over_ranks(time.perf_counter() - t0)
+        rec.update({"inverse_plus_gradient_s": t_g, "objective_evaluation_with_gradient_s": t_f + t_s + t_g,
+                    "evaluation_tflops_per_gpu_on_N3": float(n) ** 3 / (t_f + t_s + t_g) / 1e12 / ctx.world,
+                    "evaluation_frac_fp64_peak_per_gpu": float(n) ** 3 / (t_f + t_s + t_g) / 1e12 / ctx.world / peak,
+                    "inverse_bcast_GB_this_rank": (ops.bcast_bytes - b0) / 1e9,
+                    "grad_log_noise": g_noise, "grad_log_length_scale_0": float(g_ls[0])})
         if n == 20000:
-            ref, *_ = est._engine.lml(inv_ls, 1.0, noise, False)
+            ref, _, gls_ref, gn_ref = est._engine.lml(inv_ls, 1.0, noise, True)
             rec["check_lml_rel_vs_single_gpu_engine"] = abs(lml - ref) / abs(ref)
+            rec["check_grad_maxrel_vs_single_gpu_engine"] = float(max(np.max(np.abs(g_ls - gls_ref)) / np.max(np.abs(gls_ref)),
+                                                                     abs(g_noise - gn_ref) / abs(gn_ref)))
         out[f"N{n // 1000}k"] = rec
+        gp.release_inverse()
         del gp, ops
         torch.cuda.empty_cache()
     return out

@@ -232,43 +232,66 @@ template <int DP, int TT>
 __global__ void __launch_bounds__(256, 2) gpk_predict_mean_fused_kernel(
     const double* __restrict__ Xq, int ldq, int Mq, const double* __restrict__ X, int ldx, int N, GpkKernelParams p,
     const double* __restrict__ alpha, int lda, int t0, int T, double* __restrict__ partial, int MP, int tiles_per_split) {
-  __shared__ double xi[KTILE][DP + 1], xj[KTILE][DP + 1], aj[KTILE][TT + 1];
+  // training rows and their alpha rows are double-buffered: the next step's global loads are issued before this
+  // step's arithmetic and parked in registers, so their latency hides behind ~700 FP64 instructions per thread
+  __shared__ double xj[2][KTILE][DP + 1], aj[2][KTILE][TT + 1];
   const int tid = threadIdx.x, tx = tid & 7, ty = tid >> 3;      // 32 x 8 threads: query rows ty, ty+32; columns tx+8b
   const int i0 = blockIdx.x * KTILE, split = blockIdx.y;
   const int ntiles = (N + KTILE - 1) / KTILE;
   const int jt0 = split * tiles_per_split, jt1 = min(ntiles, jt0 + tiles_per_split);
-  load_scaled_rows<DP>(xi, Xq, ldq, i0, Mq, p, tid);
-  __syncthreads();
-  double xq0[DP], xq1[DP], acc0[TT], acc1[TT];
+  constexpr int NX = (KTILE * DP + 255) / 256, NA = (KTILE * TT + 255) / 256;   // staged elements per thread
+  double px[NX], pa[NA];
+  auto fetch = [&](int jt) {          // global -> registers (scaled inputs, alpha; zero beyond N / T)
+    const int j0 = jt * KTILE;
 #pragma unroll
-  for (int d = 0; d < DP; ++d) { xq0[d] = xi[ty][d]; xq1[d] = xi[ty + 32][d]; }
+    for (int u = 0; u < NX; ++u) {
+      const int idx = tid + 256 * u, r = idx / DP, d = idx % DP;
+      px[u] = (idx < KTILE * DP && j0 + r < N && d < p.D) ? X[(size_t)(j0 + r) * ldx + d] * p.inv_ls[d] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < NA; ++u) {
+      const int idx = tid + 256 * u, r = idx / TT, t = idx % TT;
+      pa[u] = (idx < KTILE * TT && j0 + r < N && t0 + t < T) ? alpha[(size_t)(j0 + r) * lda + t0 + t] : 0.0;
+    }
+  };
+  auto park = [&](int buf) {          // registers -> shared
+#pragma unroll
+    for (int u = 0; u < NX; ++u) { const int idx = tid + 256 * u; if (idx < KTILE * DP) xj[buf][idx / DP][idx % DP] = px[u]; }
+#pragma unroll
+    for (int u = 0; u < NA; ++u) { const int idx = tid + 256 * u; if (idx < KTILE * TT) aj[buf][idx / TT][idx % TT] = pa[u]; }
+  };
+  if (jt0 < jt1) { fetch(jt0); park(0); }
+  __syncthreads();
+  double xq0[DP], xq1[DP], acc0[TT], acc1[TT];   // this thread's two query rows, scaled, straight from global (once)
+#pragma unroll
+  for (int d = 0; d < DP; ++d) {
+    const bool dv = d < p.D;
+    xq0[d] = (dv && i0 + ty < Mq) ? Xq[(size_t)(i0 + ty) * ldq + d] * p.inv_ls[d] : 0.0;
+    xq1[d] = (dv && i0 + ty + 32 < Mq) ? Xq[(size_t)(i0 + ty + 32) * ldq + d] * p.inv_ls[d] : 0.0;
+  }
 #pragma unroll
   for (int t = 0; t < TT; ++t) acc0[t] = acc1[t] = 0.0;
   for (int jt = jt0; jt < jt1; ++jt) {
-    const int j0 = jt * KTILE;
-    __syncthreads();                       // the previous step's xj / aj are no longer read
-    load_scaled_rows<DP>(xj, X, ldx, j0, N, p, tid);
-    for (int idx = tid; idx < KTILE * TT; idx += 256) {
-      const int r = idx / TT, t = idx % TT;
-      aj[r][t] = (j0 + r < N && t0 + t < T) ? alpha[(size_t)(j0 + r) * lda + t0 + t] : 0.0;   // padding rows add 0
-    }
-    __syncthreads();
+    const int cur = (jt - jt0) & 1;
+    if (jt + 1 < jt1) fetch(jt + 1);
 #pragma unroll 2
     for (int b = 0; b < 8; ++b) {
       const int lj = tx + 8 * b;
       double d20 = 0.0, d21 = 0.0;
 #pragma unroll
       for (int d = 0; d < DP; ++d) {
-        const double x = xj[lj][d], f0 = xq0[d] - x, f1 = xq1[d] - x;
+        const double x = xj[cur][lj][d], f0 = xq0[d] - x, f1 = xq1[d] - x;
         d20 += f0 * f0; d21 += f1 * f1;
       }
       const double k0 = exp(-0.5 * d20), k1 = exp(-0.5 * d21);
 #pragma unroll
       for (int t = 0; t < TT; ++t) {
-        const double av = aj[lj][t];
+        const double av = aj[cur][lj][t];
         acc0[t] = fma(k0, av, acc0[t]); acc1[t] = fma(k1, av, acc1[t]);
       }
     }
+    if (jt + 1 < jt1) park(cur ^ 1);   // the other buffer was last read in step jt - 1, behind the barrier below
+    __syncthreads();
   }
 #pragma unroll
   for (int t = 0; t < TT; ++t) {
