@@ -37,7 +37,9 @@ int gpk_gram(const double* X_d, int N, int D, const double* inv_ls_h, double c, 
 
 /* scipy.linalg.cholesky (dpotrf) at _gpr.py:352,591 fused with the triangular inverse.
  * A_d in: lower triangle of K, out: lower factor L; the 128-blocks strictly above the diagonal of A_d are used as
- * scratch.  Mlow_d = L^-1 (lower), Mup_d = L^-T (upper).  One enqueue at a time per device (internal mutex: the
+ * scratch.  Mlow_d = L^-1 (lower), Mup_d = L^-T (upper): only the triangle is written -- the 128-blocks strictly above
+ * Mlow_d's block diagonal and strictly below Mup_d's keep whatever the buffers held (inside the diagonal 128-blocks the
+ * other triangle is explicit zeros), so a consumer either passes the matching tri hint to gpk_gemm_nt or masks.  One enqueue at a time per device (internal mutex: the
  * recursion's side streams are per device); safe to call from several host threads. */
 int gpk_potrf_inv(double* A_d, double* Mlow_d, double* Mup_d, int NP, int* info_d, void* stream);
 

@@ -53,6 +53,7 @@ class NumpyOps:
     def to_host(self, a): return np.array(a)
     def zero(self, a): a[...] = 0.0
     def copy(self, src, dst): dst[...] = src
+    def copy_triu(self, src, dst): dst[...] = np.triu(src)
     def sync(self): pass
 
     def gram_block(self, Xq, mq, Xc, nc, D, inv_ls, c, out, MP, NB):
@@ -75,6 +76,14 @@ class NumpyOps:
         A[...] = L
         Ml[...] = np.linalg.inv(L)
         Mu[...] = Ml.T
+        # like the device kernel, leave garbage (not zeros) in the 128-blocks the recursion never writes:
+        # strictly above Mlow's block diagonal, strictly below Mup's
+        nb = NB // 128
+        for bi in range(nb):
+            for bj in range(nb):
+                blk = (slice(128 * bi, 128 * bi + 128), slice(128 * bj, 128 * bj + 128))
+                if bj > bi: Ml[blk] = np.nan
+                if bj < bi: Mu[blk] = np.nan
 
     def gemm_nt(self, A, B, Cm, M, N, K, alpha, acc, b_tri=0):
         Bm = np.tril(B[:N, :K]) if b_tri == 1 else B[:N, :K]

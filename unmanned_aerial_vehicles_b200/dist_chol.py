@@ -137,6 +137,10 @@ class CudaOps:
     def zero(self, a):
         a.zero_()
 
+    def copy_triu(self, src, dst):
+        """dst = upper triangle of src, zeros below the diagonal"""
+        dst.copy_(self.t.triu(src))
+
     def gemv(self, A, v, out, alpha, beta, transpose):
         M, K = A.shape
         _lib.check(self.lib.gpk_gemv(self._p(A), A.stride(0), M, K, self._p(v), v.shape[1], self._p(out), alpha, beta,

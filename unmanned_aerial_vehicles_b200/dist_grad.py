@@ -73,7 +73,9 @@ class DistGradMixin:
                     dst = self.rowbuf[b][p * NB:(p + 1) * NB]
                     slot = self.mt[j][:, (lk - self.lfirst(j)) * NB:(lk - self.lfirst(j) + 1) * NB]
                     if j == k:
-                        o.copy(self.Mu[k], dst)                      # Mt(k,k) = (L_kk^-1)^T
+                        # Mt(k,k) = (L_kk^-1)^T; potrf_inv leaves the 128-blocks below Mup's diagonal unwritten
+                        # and this tile is a FULL operand of the updates below: take the triangle only
+                        o.copy_triu(self.Mu[k], dst)
                     else:
                         o.gemm_nt(slot, self.mlrow, dst, NB, NB, NB, 1.0, 0, b_tri=1)
                         self.inv_flops += float(NB) ** 3
