@@ -361,11 +361,14 @@ def extra_dist_chol(ctx, est, peak):
     torch = ctx.torch
     th = theta_sequence(0, 1)[0]
     inv_ls, noise = np.exp(-th[:D]), float(np.exp(th[D]))
-    out = {"grid": "x".join(map(str, default_grid(ctx.world))), "NB": 2048}
+    grid = default_grid(ctx.world)
+    if os.environ.get("GPK_DIST_GRID"):                       # e.g. GPK_DIST_GRID=1x8 (tools/dist_chol_run.py sweeps it)
+        grid = tuple(int(v) for v in os.environ["GPK_DIST_GRID"].split("x"))
+    out = {"grid": "x".join(map(str, grid)), "NB": 2048}
     sizes = [20000] + ([{2: 100000, 4: 140000, 8: 200000}.get(ctx.world, 20000 * ctx.world)] if ctx.world > 1 else [])
     for n in sizes:
         X, Y = make_data(n)
-        gp = DistGP(X, Y, JITTER, NB=2048)
+        gp = DistGP(X, Y, JITTER, NB=2048, grid=grid)
         ops = gp.ops
         ctx.barrier()
         ops.bcast_bytes = ops.bcast_calls = 0

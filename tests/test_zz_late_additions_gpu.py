@@ -137,3 +137,21 @@ def test_residual_metrics_reduced_on_device_match_numpy(m):
             np.testing.assert_allclose(dev["per_component"][col], host["per_component"][col], rtol=1e-8, atol=1e-12)
         assert dev["global"]["mse_gp"] == pytest.approx(host["global"]["mse_gp"], rel=1e-9)
         assert dev["fractions"] == pytest.approx(host["fractions"], abs=1e-12)
+
+
+@pytest.mark.gpu
+def test_copy_kernels_take_more_than_65535_rows():
+    """the row index of the copy kernels lives in grid.x (grid.y stops at 65535): a 70 000-row pad-copy must launch and
+    be exact -- the same indexing serves gpk_extract_lower (the L_ download) and the L21 copy of the recursion"""
+    import ctypes as C
+    import torch
+    from unmanned_aerial_vehicles_b200 import _lib
+    lib = _lib.load()
+    R, Cc, RP, CP = 70000, 5, 70016, 128
+    src = torch.arange(R * Cc, dtype=torch.float64, device="cuda").reshape(R, Cc)
+    dst = torch.full((RP, CP), -1.0, dtype=torch.float64, device="cuda")
+    rc = lib.gpk_pad_copy(C.c_void_p(src.data_ptr()), R, Cc, C.c_void_p(dst.data_ptr()), RP, CP,
+                          C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.equal(dst[:R, :Cc], src) and float(dst[R:].abs().sum()) == 0.0 and float(dst[:, Cc:].abs().sum()) == 0.0

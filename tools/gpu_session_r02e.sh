@@ -1,0 +1,28 @@
+#!/usr/bin/env bash
+# Round-2 EIGHT-GPU session, one call:   gpurun --gpus 8 --timeout 1500 -- 'bash tools/gpu_session_r02e.sh'
+# Everything that needs 8 GPUs, most important first; every step under its own timeout; results gpurun_out/r02e_*.
+set -u
+mkdir -p gpurun_out
+step() {  # name, timeout seconds, command...
+  local name=$1 lim=$2; shift 2
+  local t0=$(date +%s)
+  timeout "$lim" "$@" > "gpurun_out/r02e_${name}.out" 2> "gpurun_out/r02e_${name}.err"
+  echo "{\"step\": \"${name}\", \"rc\": $?, \"s\": $(( $(date +%s) - t0 ))}" | tee -a gpurun_out/r02e_session.jsonl
+}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
+: > gpurun_out/r02e_session.jsonl
+nvidia-smi --query-gpu=index,name --format=csv > gpurun_out/r02e_gpu.csv 2>&1
+# 0. the GPU suite (one GPU; the NCCL test takes two): the distributed-gradient fix and the double-buffered mean kernel
+step pytest_gpu 900 python -m pytest tests -m gpu -x -q
+# 1. the bench line at 8 GPUs: sharded 10-restart fit, row-sharded predict, N=200k factor + gradient
+step bench8 900 $TR --master-port 29541 bench.py --gpus 8 --steps 5 --warmup 3
+# 2. config 5 variants with the per-phase trace (grid / block size), the first with the distributed gradient + predict
+step dist200k_2x4_grad 600 $TR --master-port 29542 tools/dist_chol_run.py --size 200000 --grid 2x4 --trace --grad --predict-rows 4096
+step dist200k_1x8 300 $TR --master-port 29543 tools/dist_chol_run.py --size 200000 --grid 1x8 --trace
+step dist200k_2x4_nb1024 300 $TR --master-port 29544 tools/dist_chol_run.py --size 200000 --grid 2x4 --block 1024 --trace
+step dist200k_4x2 300 $TR --master-port 29545 tools/dist_chol_run.py --size 200000 --grid 4x2 --trace
+# 3. config 4, truncated: one output x 8 runs x 3 L-BFGS-B iterations at N=50k (60 GB per model per GPU)
+step config4_trunc 600 $TR --master-port 29546 tools/config4_run.py --size 50000 --restarts 7 --outputs 1 --maxiter 3
+# 4. the same at two outputs, to see the buffers released between outputs
+step config4_trunc2 600 $TR --master-port 29547 tools/config4_run.py --size 50000 --restarts 7 --outputs 2 --maxiter 1
+cat gpurun_out/r02e_session.jsonl
