@@ -155,3 +155,28 @@ def test_copy_kernels_take_more_than_65535_rows():
     assert rc == 0
     torch.cuda.synchronize()
     assert torch.equal(dst[:R, :Cc], src) and float(dst[R:].abs().sum()) == 0.0 and float(dst[:, Cc:].abs().sum()) == 0.0
+
+
+@pytest.mark.gpu
+def test_distributed_fit_single_rank_on_device_equals_the_single_gpu_fit():
+    """dist_fit.DistributedGPR through libgpk.so (one rank: the block-cyclic layout with a 1x1 grid) against the
+    single-GPU estimator with the same optimiser: same theta*, LML and predictions"""
+    import warnings
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+    from unmanned_aerial_vehicles_b200 import GaussianProcessRegressor
+    from unmanned_aerial_vehicles_b200.dist_fit import DistributedGPR
+    rng = np.random.default_rng(12)
+    X = rng.standard_normal((1500, 5))
+    y = np.sin(X @ rng.standard_normal(5) / 2) + 0.1 * rng.standard_normal(1500) + 3.0
+    k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 5, (0.1, 10.0)) + WhiteKernel(0.05, (1e-5, 10.0))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        e = GaussianProcessRegressor(kernel=k, alpha=1e-6, normalize_y=True).fit(X, y)
+        g = DistributedGPR(k, alpha=1e-6, normalize_y=True, NB=512).fit(X, y)
+    np.testing.assert_allclose(g.kernel_.theta, e.kernel_.theta, rtol=0, atol=1e-5)
+    assert abs(g.log_marginal_likelihood_value_ - e.log_marginal_likelihood_value_) <= 1e-8 * abs(e.log_marginal_likelihood_value_)
+    me, se = e.predict(X[:100] + 0.03, return_std=True)
+    mg, sg = g.predict(X[:100] + 0.03, return_std=True)
+    assert mg.shape == me.shape and sg.shape == se.shape
+    np.testing.assert_allclose(mg, me, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(sg, se, rtol=0, atol=1e-6)
