@@ -25,4 +25,6 @@ step dist200k_4x2 300 $TR --master-port 29545 tools/dist_chol_run.py --size 2000
 step config4_trunc 600 $TR --master-port 29546 tools/config4_run.py --size 50000 --restarts 7 --outputs 1 --maxiter 3
 # 4. the same at two outputs, to see the buffers released between outputs
 step config4_trunc2 600 $TR --master-port 29547 tools/config4_run.py --size 50000 --restarts 7 --outputs 2 --maxiter 1
+# 5. an N=200k hyper-parameter FIT (truncated to one L-BFGS-B iteration: 2-3 objective evaluations with gradient)
+step dist_fit200k 900 $TR --master-port 29548 tools/dist_fit_run.py --size 200000 --maxiter 1 --grid 2x4
 cat gpurun_out/r02e_session.jsonl
