@@ -537,12 +537,14 @@ def b200_arm(args):
             line["extra"][name] = res
 
     # the single-GPU predict figure of the metric (config 3's chunk: 4096 trajectories x 20 steps)
+    # (the estimator's engine stays alive: the distributed extra checks itself against it; the riskiest extra -- the
+    #  one with the most collectives -- runs last, so a hang there costs nothing that was already measured)
     run_extra("predict_sharded", lambda: extra_predict_sharded(ctx, est, args.predict_rows, peak_all))
+    run_extra("full_fit", lambda: extra_full_fit(ctx, X, Y))
     run_extra("dist_chol", lambda: extra_dist_chol(ctx, est, peak_all))
     eng = None
     est._engine = None
     torch.cuda.empty_cache()
-    run_extra("full_fit", lambda: extra_full_fit(ctx, X, Y))
     if line is not None:
         ps = line["extra"].get("predict_sharded") or {}
         if "mean_std_pts_per_s" in ps:       # the metric's three quantities, side by side
@@ -575,7 +577,7 @@ def main():
     ap.add_argument("--predict-rows", type=int, default=81920, help="query rows per GPU of the predict extra")
     ap.add_argument("--skip", default="", help="comma list of extras to leave out: predict_sharded, dist_chol, "
                                                "full_fit, cpu_baseline")
-    ap.add_argument("--extras-deadline-s", type=float, default=1500.0)
+    ap.add_argument("--extras-deadline-s", type=float, default=900.0)
     ap.add_argument("--cpu-budget-s", type=float, default=100.0,
                     help="reference arm: full evaluations are repeated while their total stays under this")
     ap.add_argument("--no-cpu-baseline", action="store_true")
