@@ -39,8 +39,8 @@ __global__ void __launch_bounds__(256, 2) gpk_gram_kernel(const double* __restri
     double out[4];
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
-      const int lj = tx * 4 + b, j = j0 + lj;
-      double d2 = 0.0;
+      const int lj = tx + 16 * b, j = j0 + lj;    // cyclic columns: lanes read xj with an odd row stride (no bank
+      double d2 = 0.0;                            // conflicts) and store 16 consecutive doubles per row
 #pragma unroll
       for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; d2 += df * df; }
       double v;
@@ -49,9 +49,9 @@ __global__ void __launch_bounds__(256, 2) gpk_gram_kernel(const double* __restri
       else v = p.c * exp(-0.5 * d2);
       out[b] = v;
     }
-    double* dst = K + (size_t)i * ldk + j0 + tx * 4;
-    *reinterpret_cast<double2*>(dst) = make_double2(out[0], out[1]);
-    *reinterpret_cast<double2*>(dst + 2) = make_double2(out[2], out[3]);
+    double* dst = K + (size_t)i * ldk + j0 + tx;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) dst[16 * b] = out[b];
   }
 }
 
@@ -72,15 +72,15 @@ __global__ void __launch_bounds__(256, 2) gpk_cross_gram_kernel(const double* __
     double out[4];
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
-      const int lj = tx * 4 + b, j = j0 + lj;
+      const int lj = tx + 16 * b, j = j0 + lj;    // cyclic columns (see gpk_gram_kernel)
       double d2 = 0.0;
 #pragma unroll
       for (int d = 0; d < DP; ++d) { double df = xi[li][d] - xj[lj][d]; d2 += df * df; }
       out[b] = (i < Mq && j < N) ? p.c * exp(-0.5 * d2) : 0.0;
     }
-    double* dst = Ks + (size_t)i * ldk + j0 + tx * 4;
-    *reinterpret_cast<double2*>(dst) = make_double2(out[0], out[1]);
-    *reinterpret_cast<double2*>(dst + 2) = make_double2(out[2], out[3]);
+    double* dst = Ks + (size_t)i * ldk + j0 + tx;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) dst[16 * b] = out[b];
   }
 }
 
@@ -120,12 +120,11 @@ __global__ void __launch_bounds__(256) gpk_grad_kernel(const double* __restrict_
     for (int a = 0; a < 4; ++a) {
       const int li = ty * 4 + a, i = i0 + li;
       const long long gi = gi0 + i;
-      const double* kr = Kinv + (size_t)i * ldk + j0 + tx * 4;
-      double2 k01 = *reinterpret_cast<const double2*>(kr), k23 = *reinterpret_cast<const double2*>(kr + 2);
-      double kin[4] = {k01.x, k01.y, k23.x, k23.y};
+      const double* kr = Kinv + (size_t)i * ldk + j0 + tx;      // cyclic columns: 16 lanes read 128 contiguous bytes
+      double kin[4] = {kr[0], kr[16], kr[32], kr[48]};
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        const int lj = tx * 4 + b, j = j0 + lj;
+        const int lj = tx + 16 * b, j = j0 + lj;
         const long long gj = gj0 + j;
         if (i >= nr || j >= nc || gj > gi) continue;
         double w = 0.0;
