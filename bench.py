@@ -309,7 +309,7 @@ def extra_full_fit(ctx, X, Y):
     per_rank = ctx.gather_obj({"rank": ctx.rank, "runs": st.get("items"), "lml_evals": int(g.n_lml_evals_),
                                "busy_s": st.get("busy_s"), "idle_s": st.get("idle_s")})
     out = {"full_fit_s_10_restarts": dt, "lml_evals_all_ranks": int(sum(p["lml_evals"] for p in per_rank)),
-           "longest_run_chain_evals": int(max(p["lml_evals"] for p in per_rank)),
+           "max_lml_evals_on_one_rank": int(max(p["lml_evals"] for p in per_rank)),
            "lml": float(g.log_marginal_likelihood_value_), "kernel": str(g.kernel_),
            "schedule": "dynamic queue over ranks" if ctx.world > 1 else "serial", "scaling": "strong",
            "per_rank": per_rank}
