@@ -55,7 +55,7 @@ cudaError_t gpk_launch_transpose_block(const double* src, int lds, double* dst, 
 static inline int gpk_current_device() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < GPK_MAX_DEV) ? d : 0; }
 
 extern unsigned long long g_gpk_launches;   // kernels launched by this library (bench.py's gpu_launches)
-#define GPK_LAUNCHED() (++g_gpk_launches)
+#define GPK_LAUNCHED() ((void)__atomic_fetch_add(&g_gpk_launches, 1ULL, __ATOMIC_RELAXED))   // host threads may launch concurrently
 // optional per-launch timing of the DMMA GEMM (bench.py roofline): event pairs around each launch
 struct GpkProfile { int enabled; int n; double flops; };
 extern GpkProfile g_gpk_prof;
