@@ -100,6 +100,24 @@ int gpk_predict_mean_fused(const double* Xq_d, int Mq, int MP, const double* X_d
                            double c, const double* alpha_d, int T, const double* y_mean_d, const double* y_std_d,
                            double* partial_d, double* mean_d, void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  gpk_predict_mean_fused with the
+ * kernel's scratch (the per-split partial sums: splits(MP, N) * MP * T doubles) taken from a file-scope device array
+ * of GPK_STATIC_SCRATCH_DOUBLES doubles (4 MiB, held by every GPU that loads the library until exit) instead of a
+ * caller buffer; inputs and outputs are still the caller's.  Allocates nothing: no cudaMalloc / cudaFree / allocating
+ * library routine.  A shape whose scratch demand exceeds the array is rejected with GPK_ERR_STATIC_SCRATCH_TOO_SMALL
+ * before anything is launched (e.g. MP * T > 524288 at one split; MP = 128 rows against N = 20000, T = 3 needs 56832).
+ * The array's device address is looked up once per device, with that device current, on the first call there
+ * (cudaGetSymbolAddress, return code checked): make that first call outside graph capture.  Every call on a device
+ * shares the array, which keeps the last call's contents -- nothing in it has to start at zero (every slot read is
+ * written first by the same call) -- so calls that OVERLAP on the GPU (two streams, two host threads) race on it:
+ * serialise them.  Same results as gpk_predict_mean_fused, bit for bit. */
+#define GPK_STATIC_SCRATCH_DOUBLES 524288
+#define GPK_ERR_STATIC_SCRATCH_TOO_SMALL (-2000)
+int gpk_predict_mean_fused_static(const double* Xq_d, int Mq, int MP, const double* X_d, int N, int D,
+                                  const double* inv_ls_h, double c, const double* alpha_d, int T,
+                                  const double* y_mean_d, const double* y_std_d, double* mean_d, void* stream);
+
 /* _gpr.py:460-500: V = Ks L^-T, var = prior - rowsum(V^2) clamped at 0, std = sqrt(var * y_std^2).
  * rowsq_d: scratch MP x (NP/64).  *neg_d is incremented per clamped row (the caller warns). */
 int gpk_predict_std(const double* Ks_d, int Mq, int MP, const double* Mlow_d, int NP, double prior,

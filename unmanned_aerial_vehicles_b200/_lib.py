@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("GPK_LIB", os.path.join(_HERE, "libgpk.so"))
 SYMBOLS = (
     "gpk_abi_version", "gpk_pad", "gpk_lml_out_len", "gpk_grad_workspace_doubles", "gpk_gram",
     "gpk_potrf_inv", "gpk_potrs", "gpk_lauum", "gpk_lml_grad", "gpk_lml_eval", "gpk_cross_gram",
-    "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict_mean_workspace_doubles", "gpk_predict_mean_fused", "gpk_predict", "gpk_predict_stacked", "gpk_residual_metrics_out_len", "gpk_residual_metrics_workspace_doubles", "gpk_residual_metrics", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
+    "gpk_predict_mean", "gpk_predict_std", "gpk_predict_workspace_doubles", "gpk_predict_mean_workspace_doubles", "gpk_predict_mean_fused", "gpk_predict_mean_fused_static", "gpk_predict", "gpk_predict_stacked", "gpk_residual_metrics_out_len", "gpk_residual_metrics_workspace_doubles", "gpk_residual_metrics", "gpk_extract_lower", "gpk_pad_copy", "gpk_gemm_nt",
     "gpk_dmma_probe", "gpk_launch_count", "gpk_profile_begin", "gpk_profile_end", "gpk_profile_launch", "gpk_leaf_phase_cycles", "gpk_gemv", "gpk_trimv", "gpk_fix_diag", "gpk_logdiag",
     "gpk_grad_block_workspace_doubles", "gpk_grad_padded_dim", "gpk_grad_block", "gpk_grad_block_sum",
 )
@@ -37,6 +37,8 @@ _dp = C.POINTER(C.c_double)
 
 
 MAX_STACKED = 16   # GPK_MAX_STACKED in include/gpk.h
+STATIC_SCRATCH_DOUBLES = 524288           # GPK_STATIC_SCRATCH_DOUBLES
+ERR_STATIC_SCRATCH_TOO_SMALL = -2000      # GPK_ERR_STATIC_SCRATCH_TOO_SMALL
 
 
 class StackedModel(C.Structure):
@@ -66,6 +68,7 @@ def _declare(lib):
     lib.gpk_predict_mean_workspace_doubles.argtypes = [_i, _i, _i, _i]
     lib.gpk_predict_mean_workspace_doubles.restype = C.c_size_t
     lib.gpk_predict_mean_fused.argtypes = [_p, _i, _i, _p, _i, _i, _dp, _d, _p, _i, _p, _p, _p, _p, _p]
+    lib.gpk_predict_mean_fused_static.argtypes = [_p, _i, _i, _p, _i, _i, _dp, _d, _p, _i, _p, _p, _p, _p]
     lib.gpk_predict.argtypes = [_p, _i, _i, _p, _i, _dp, _d, _d, _p, _i, _p, _i, _p, _p, _p, _p, _p, _p, C.c_size_t, _p]
     lib.gpk_predict_stacked.argtypes = [C.POINTER(StackedModel), _i, _i, _p]
     lib.gpk_residual_metrics_workspace_doubles.argtypes = [_i]
