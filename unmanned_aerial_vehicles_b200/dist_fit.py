@@ -31,10 +31,11 @@ class DistributedGPR:
     the distributed factor.  ``maxiter`` truncates each L-BFGS-B run (None: SciPy's default, as sklearn)."""
 
     def __init__(self, kernel, *, alpha=1e-10, optimizer="fmin_l_bfgs_b", n_restarts_optimizer=0, normalize_y=False,
-                 random_state=None, maxiter=None, NB=2048, grid=None, ops=None, lookahead=True):
+                 random_state=None, maxiter=None, maxfun=None, on_eval=None, NB=2048, grid=None, ops=None, lookahead=True):
         self.kernel, self.alpha, self.optimizer = kernel, alpha, optimizer
         self.n_restarts_optimizer, self.normalize_y, self.random_state = n_restarts_optimizer, normalize_y, random_state
         self.maxiter, self.NB, self.grid, self.ops, self.lookahead = maxiter, NB, grid, ops, lookahead
+        self.maxfun, self.on_eval = maxfun, on_eval      # cap on objective evaluations per run; callback(k, lml, s)
 
     def fit(self, X, y):
         X = np.ascontiguousarray(X, dtype=np.float64)
@@ -62,6 +63,8 @@ class DistributedGPR:
             lml, g_c, g_ls, g_noise = self._gp.lml_grad(1.0 / low.length_scale, low.c, low.noise)
             self.n_lml_evals_ += 1
             self.evaluation_seconds_.append(time.perf_counter() - t0)
+            if self.on_eval is not None:
+                self.on_eval(self.n_lml_evals_, float(lml), self.evaluation_seconds_[-1])
             if not np.isfinite(lml):
                 return np.inf, np.zeros(len(low.theta_map))    # _gpr.py:592-593
             return -lml, -assemble_gradient(low, g_c, g_ls, g_noise)
@@ -72,6 +75,8 @@ class DistributedGPR:
             starts = [self.kernel_.theta] + [rng.uniform(bounds[:, 0], bounds[:, 1])
                                              for _ in range(self.n_restarts_optimizer)]   # _gpr.py:312-333
             opts = {} if self.maxiter is None else {"maxiter": int(self.maxiter)}
+            if self.maxfun is not None:
+                opts["maxfun"] = int(self.maxfun)
             optima = []
             for t0 in starts:
                 with warnings.catch_warnings():
