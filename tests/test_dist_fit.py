@@ -57,6 +57,13 @@ def test_distributed_fit_single_rank_matches_sklearn():
     g1 = DistributedGPR(k, alpha=1e-6, maxiter=2, NB=128, ops=NumpyGradOps()).fit(X, Y[:, 0])
     assert g1.predict(X[:4]).shape == (4,) and g1.predict(X[:4], return_std=True)[1].shape == (4,)
     assert g1.n_lml_evals_ <= 8
+    # maxfun is a hard cap (SciPy's own is only checked between iterations): exactly 2 evaluations, best one kept
+    seen = []
+    g2 = DistributedGPR(k, alpha=1e-6, maxfun=2, on_eval=lambda kk, lml, sec: seen.append((kk, lml)), NB=128,
+                        ops=NumpyGradOps()).fit(X, Y[:, 0])
+    assert g2.n_lml_evals_ == 2 and [kk for kk, _ in seen] == [1, 2]
+    assert g2.log_marginal_likelihood_value_ == max(l for _, l in seen)
+    assert g2.predict(X[:4]).shape == (4,)                                        # the final factor is in place
     fixed = DistributedGPR(k, alpha=1e-6, optimizer=None, NB=128, ops=NumpyGradOps()).fit(X, Y)
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")

@@ -26,9 +26,16 @@ from .dist_chol import DistGP
 from .kernel_lowering import assemble_gradient, lower
 
 
+class _EvaluationBudgetSpent(Exception):
+    pass
+
+
 class DistributedGPR:
     """sklearn-surface subset (fit / predict / log_marginal_likelihood / kernel_ / log_marginal_likelihood_value_) over
-    the distributed factor.  ``maxiter`` truncates each L-BFGS-B run (None: SciPy's default, as sklearn)."""
+    the distributed factor.  ``maxiter`` truncates each L-BFGS-B run (None: SciPy's default, as sklearn).  ``maxfun`` is
+    a HARD cap on the objective evaluations of one run: SciPy's own ``maxfun`` is only checked between iterations (its
+    line search went to four evaluations under ``maxfun=2`` in the N=200k run of profiles/r02i_*), so the objective
+    itself stops the run after the cap and the best point evaluated so far is taken as that run's result."""
 
     def __init__(self, kernel, *, alpha=1e-10, optimizer="fmin_l_bfgs_b", n_restarts_optimizer=0, normalize_y=False,
                  random_state=None, maxiter=None, maxfun=None, on_eval=None, NB=2048, grid=None, ops=None, lookahead=True):
@@ -56,8 +63,12 @@ class DistributedGPR:
         self.n_lml_evals_ = 0
         self.evaluation_seconds_ = []
 
+        run = {"evals": 0, "best": None}          # per L-BFGS-B run: evaluations so far, (f, theta) of the best one
+
         def obj_func(theta):
             import time
+            if self.maxfun is not None and run["evals"] >= int(self.maxfun):
+                raise _EvaluationBudgetSpent()
             t0 = time.perf_counter()
             low = template.with_theta(theta)
             lml, g_c, g_ls, g_noise = self._gp.lml_grad(1.0 / low.length_scale, low.c, low.noise)
@@ -65,6 +76,9 @@ class DistributedGPR:
             self.evaluation_seconds_.append(time.perf_counter() - t0)
             if self.on_eval is not None:
                 self.on_eval(self.n_lml_evals_, float(lml), self.evaluation_seconds_[-1])
+            run["evals"] += 1
+            if np.isfinite(lml) and (run["best"] is None or -lml < run["best"][0]):
+                run["best"] = (-float(lml), np.array(theta, dtype=np.float64))
             if not np.isfinite(lml):
                 return np.inf, np.zeros(len(low.theta_map))    # _gpr.py:592-593
             return -lml, -assemble_gradient(low, g_c, g_ls, g_noise)
@@ -75,14 +89,18 @@ class DistributedGPR:
             starts = [self.kernel_.theta] + [rng.uniform(bounds[:, 0], bounds[:, 1])
                                              for _ in range(self.n_restarts_optimizer)]   # _gpr.py:312-333
             opts = {} if self.maxiter is None else {"maxiter": int(self.maxiter)}
-            if self.maxfun is not None:
-                opts["maxfun"] = int(self.maxfun)
             optima = []
             for t0 in starts:
-                with warnings.catch_warnings():
-                    warnings.simplefilter("ignore")
-                    r = scipy.optimize.minimize(obj_func, t0, method="L-BFGS-B", jac=True, bounds=bounds, options=opts)
-                optima.append((r.x, r.fun))
+                run["evals"], run["best"] = 0, None
+                try:
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore")
+                        r = scipy.optimize.minimize(obj_func, t0, method="L-BFGS-B", jac=True, bounds=bounds, options=opts)
+                    optima.append((r.x, r.fun))
+                except _EvaluationBudgetSpent:            # raised identically on every rank: same values everywhere
+                    if run["best"] is None:
+                        raise np.linalg.LinAlgError("no finite objective value within the evaluation budget")
+                    optima.append((run["best"][1], run["best"][0]))
             best = int(np.argmin(list(map(itemgetter(1), optima))))
             self.kernel_.theta = optima[best][0]
             self.log_marginal_likelihood_value_ = -float(optima[best][1])
