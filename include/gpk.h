@@ -191,7 +191,8 @@ int gpk_fix_diag(double* A_d, int lda, int n, int n_valid, double add, double pa
 /* *sum_d += sum_i log A[i,i], i < n */
 int gpk_logdiag(const double* A_d, int lda, int n, double* sum_d, void* stream);
 
-/* instrumentation for bench.py: kernels launched so far by this library; and per-launch CUDA-event timing of
+/* instrumentation for bench.py (process-global state, NOT thread-safe: one profiling session at a time, and no other
+ * thread enqueuing through this library while it is on): kernels launched so far by this library; and per-launch CUDA-event timing of
  * the DMMA GEMM (dominant kernel): begin, run the step, end -> summed launch durations, executed tile flops. */
 unsigned long long gpk_launch_count(void);
 int gpk_profile_begin(void);

@@ -53,6 +53,16 @@ def test_distributed_fit_single_rank_matches_sklearn():
     np.testing.assert_allclose(gr_g, gr_s, rtol=1e-6, atol=1e-8)
     assert g.log_marginal_likelihood(th) == pytest.approx(lml_s, rel=1e-9)
     np.testing.assert_allclose(g.predict(X[:3]), s.predict(X[:3]), rtol=1e-4, atol=1e-6)   # fitted factor restored
+    # pickle: host NumPy only, no factor inside; the loaded model re-factors on first use and answers the same
+    import pickle
+    blob = pickle.dumps({"gp_model": g, "is_trained": True})             # train_gp_offline.py:188-197 schema
+    assert len(blob) < 40 * X.nbytes                                     # X, y, kernel -- not an N x N matrix
+    back = pickle.loads(blob)["gp_model"]
+    assert back._gp is None and back.ops is None
+    back.ops = NumpyGradOps()
+    for a_, b_ in zip(back.predict(X[:9] + 0.05, return_std=True), g.predict(X[:9] + 0.05, return_std=True)):
+        np.testing.assert_allclose(a_, b_, rtol=1e-12, atol=1e-14)
+    assert back.log_marginal_likelihood() == g.log_marginal_likelihood() and str(back.kernel_) == str(g.kernel_)
     # truncated run and 1-D targets (single-output models of gp_trainer.py:169-176)
     g1 = DistributedGPR(k, alpha=1e-6, maxiter=2, NB=128, ops=NumpyGradOps()).fit(X, Y[:, 0])
     assert g1.predict(X[:4]).shape == (4,) and g1.predict(X[:4], return_std=True)[1].shape == (4,)

@@ -59,6 +59,7 @@ class DistributedGPR:
         self.kernel_ = clone(self.kernel)
         self.n_features_in_ = X.shape[1]
         template = lower(self.kernel_, X.shape[1])
+        self.X_train_, self.y_train_ = X, (y2d[:, 0] if self._y_1d else y2d)
         self._gp = DistGP(X, y2d, float(self.alpha), NB=self.NB, grid=self.grid, ops=self.ops, lookahead=self.lookahead)
         self.n_lml_evals_ = 0
         self.evaluation_seconds_ = []
@@ -121,6 +122,7 @@ class DistributedGPR:
         if theta is None:
             return self.log_marginal_likelihood_value_
         low = lower(self.kernel_, self.n_features_in_).with_theta(theta)
+        self._ensure_factored()
         gp = self._gp
         if eval_gradient:
             lml, g_c, g_ls, g_noise = gp.lml_grad(1.0 / low.length_scale, low.c, low.noise)
@@ -136,8 +138,35 @@ class DistributedGPR:
             gp.solve()
         return out
 
+    # -- pickling: host NumPy only (train_gp_offline.py:188-197 stores the model under ['gp_model']).  The factor is
+    # NOT stored -- it is 160 GB at N=200k -- and is rebuilt from kernel_ on the first predict after loading, on
+    # whatever process group the loading job runs in (set .ops / .grid before that to choose).
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state.pop("_gp", None)
+        state["ops"] = None              # communicators and device handles do not travel
+        state["on_eval"] = None
+        return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        self._gp = None
+
+    def _ensure_factored(self):
+        if getattr(self, "_gp", None) is not None:
+            return
+        y2d = self.y_train_[:, None] if self._y_1d else self.y_train_
+        self._gp = DistGP(self.X_train_, y2d, float(self.alpha), NB=self.NB, grid=self.grid, ops=self.ops,
+                          lookahead=self.lookahead)
+        low = lower(self.kernel_, self.n_features_in_)
+        info = self._gp.factor(1.0 / low.length_scale, low.c, low.noise)
+        if info != 0:
+            raise np.linalg.LinAlgError(f"The kernel, {self.kernel_}, is not returning a positive definite matrix.")
+        self._gp.solve()
+
     def predict(self, X, return_std=False):
         """mean [, std] with sklearn's output shapes (_gpr.py:446-500); the same rows on every rank"""
+        self._ensure_factored()
         res = self._gp.predict(X, return_std=return_std)
         mean, std = (res if return_std else (res, None))
         mean = mean * self._y_train_std + self._y_train_mean
