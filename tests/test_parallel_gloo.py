@@ -233,3 +233,67 @@ def test_outputs_in_turn_with_restarts_sharded_equal_the_serial_fits():
             np.testing.assert_allclose(th, th0, rtol=0, atol=1e-12)
             assert lml == pytest.approx(lml0, rel=1e-12)
             np.testing.assert_allclose(pred, pred0, rtol=1e-10, atol=1e-13)
+
+
+def _run_pilot_case(pilot_rows):
+    """one ARD model, 5 optimiser runs, through parallel.fit_sharded_restarts with the pilot claim order (engine
+    double: no GPU here); returns theta*, LML, the order used and a prediction"""
+    import warnings
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel as CK, WhiteKernel
+    from test_estimator_host_logic import OracleEngine
+    from unmanned_aerial_vehicles_b200 import gpr as gpr_mod, parallel
+    real, gpr_mod.DeviceGP = gpr_mod.DeviceGP, OracleEngine
+    try:
+        X, Y = _trainer_case()
+        k = CK(1.0, constant_value_bounds="fixed") * RBF([1.0] * 4, (0.1, 10.0)) + WhiteKernel(0.01, (1e-5, 10.0))
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            g = gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, n_restarts_optimizer=4, random_state=7)
+            parallel.fit_sharded_restarts(g, X, Y[:, 0], pilot_rows=pilot_rows)
+            unseeded = gpr_mod.GaussianProcessRegressor(kernel=k, alpha=1e-6, n_restarts_optimizer=1)
+            assert parallel.pilot_order(unseeded, X, Y[:, 0], 40) is None          # its pilot would draw other starts
+            out = (g.kernel_.theta.tolist(), float(g.log_marginal_likelihood_value_), g.pilot_order_,
+                   np.asarray(g.predict(X[:3] + 0.01)).tolist(), list((parallel.last_stats or {}).get("items", [])))
+    finally:
+        gpr_mod.DeviceGP = real
+    return out
+
+
+def _pilot_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    q.put((rank, _run_pilot_case(40)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_pilot_claim_order_changes_who_runs_what_never_the_result():
+    """parallel.pilot_order: rank 0 guesses the chain lengths on a subsample and broadcasts the claim order (longest
+    first); the sharded fit must still equal the serial fit exactly, every rank must hold the same order, and every
+    run must be executed exactly once."""
+    sys.path.insert(0, ROOT)
+    serial = _run_pilot_case(None)                        # single process, no pilot: the reference result
+    assert serial[2] is None
+    single = _run_pilot_case(40)                          # single process with the pilot: same result, an order
+    assert sorted(single[2]) == [0, 1, 2, 3, 4] and single[:2] == serial[:2] and single[3] == serial[3]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pilot_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    outs = dict(q.get(timeout=300) for _ in range(2))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    assert outs[0][2] == outs[1][2] == single[2]          # the same order everywhere (rank 0's, broadcast)
+    assert sorted(outs[0][4] + outs[1][4]) == [0, 1, 2, 3, 4]
+    for r in (0, 1):
+        np.testing.assert_allclose(outs[r][0], serial[0], rtol=0, atol=1e-12)
+        assert outs[r][1] == pytest.approx(serial[1], rel=1e-12)
+        np.testing.assert_allclose(outs[r][3], serial[3], rtol=1e-10, atol=1e-13)
+    from unmanned_aerial_vehicles_b200 import parallel
+    assert parallel.run_sharded(lambda v: v * 2, [1, 2, 3], order=[2, 0, 1]) == [2, 4, 6]     # results in ITEM order
+    with pytest.raises(ValueError):
+        parallel.run_sharded(lambda v: v, [1, 2, 3], order=[0, 0, 1])

@@ -58,9 +58,12 @@ def _queue_key(group):
     return "gpk/queue/%s/%d" % ("-".join(map(str, ranks)), n)
 
 
-def run_sharded(work_fn, items, group=None, schedule="dynamic"):
+def run_sharded(work_fn, items, group=None, schedule="dynamic", order=None):
     """Run work_fn(item) over the ranks of `group`; return the results of ALL items, in item order, on every rank
     (one all_gather_object of small host objects).
+
+    order: optional permutation of range(len(items)) -- the order in which items are handed out (longest first when
+    the caller can guess lengths); it must be THE SAME on every rank.  Results stay in item order whatever it is.
 
     schedule="dynamic": items are claimed first-come through an atomic counter in the rendezvous store, so a rank
     that drew short runs takes the leftovers instead of idling; "static": round-robin (item i -> rank i % world).
@@ -69,6 +72,9 @@ def run_sharded(work_fn, items, group=None, schedule="dynamic"):
     d = _dist()
     rank, world = rank_world(group)
     items = list(items)
+    order = list(range(len(items))) if order is None else [int(i) for i in order]
+    if sorted(order) != list(range(len(items))):
+        raise ValueError("order must be a permutation of the item indices")
     t_begin = time.perf_counter()
     mine, busy, failed = {}, 0.0, None
 
@@ -82,7 +88,7 @@ def run_sharded(work_fn, items, group=None, schedule="dynamic"):
         busy += time.perf_counter() - t0
 
     if world == 1:
-        for i in range(len(items)):
+        for i in order:
             run(i)
             if failed:
                 raise ShardedWorkError(f"work item {failed.item} failed:\n{failed.text}")
@@ -96,10 +102,10 @@ def run_sharded(work_fn, items, group=None, schedule="dynamic"):
             i = int(store.add(key, 1)) - 1
             if i >= len(items):
                 break
-            run(i)
+            run(order[i])
     else:
         for i in shard_indices(len(items), rank, world):
-            run(i)
+            run(order[i])
             if failed:
                 break
     t_done = time.perf_counter()
@@ -128,10 +134,65 @@ def gather_stats(group=None):
     return out
 
 
-def fit_sharded_restarts(estimator, X, y, group=None, schedule="dynamic"):
+def pilot_order(estimator, X, y, pilot_rows, group=None, seed=0):
+    """A claim order for the optimiser runs of ``estimator.fit(X, y)``: longest chain first, the lengths GUESSED by
+    running the same fit (same kernel, same seeded starts) on a seeded subsample of ``pilot_rows`` rows -- a fit that
+    costs about a second on the GPU at 2000 rows.  On the BASELINE config-2 data the pilot's three longest chains at 500
+    and at 2000 rows contain the two 59-evaluation chains of the N=20 000 fit.  Rank 0 runs the
+    pilot and broadcasts the order, so every rank holds the same one; anything that goes wrong (an unseeded estimator,
+    whose pilot would draw other starts; an exception in the pilot) yields None = the plain queue order.  The order
+    changes who runs what and when, never the result."""
+    import numbers
+
+    d = _dist()
+    rank, world = rank_world(group)
+    order = None
+    if rank == 0:
+        try:
+            n = len(X)
+            if isinstance(getattr(estimator, "random_state", None), numbers.Integral) and 0 < pilot_rows < n \
+                    and getattr(estimator, "n_restarts_optimizer", 0) > 0:
+                from sklearn.base import clone
+
+                idx = np.sort(np.random.default_rng(seed).choice(n, int(pilot_rows), replace=False))
+                pilot = clone(estimator)
+                lens = []
+
+                def serial(run_one, starts):
+                    out = []
+                    for t0 in starts:
+                        k0 = pilot.n_lml_evals_
+                        out.append(run_one(t0))
+                        lens.append(pilot.n_lml_evals_ - k0)
+                    return out
+                pilot._restart_runner = serial
+                import warnings
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    pilot.fit(np.asarray(X)[idx], np.asarray(y)[idx])
+                pilot._engine = None
+                order = [int(i) for i in np.argsort(-np.asarray(lens), kind="stable")]
+        except Exception:          # noqa: BLE001 -- a heuristic: never in the way of the fit itself
+            order = None
+    if d is not None and world > 1:
+        box = [order]
+        d.broadcast_object_list(box, src=d.get_global_rank(group, 0) if group is not None else 0, group=group)
+        order = box[0]
+    return order
+
+
+def fit_sharded_restarts(estimator, X, y, group=None, schedule="dynamic", pilot_rows=None):
     """estimator.fit(X, y) with its 1 + n_restarts_optimizer L-BFGS-B runs sharded over the ranks of `group`.
-    Every rank ends with the same fitted estimator (same kernel_, L_, alpha_)."""
-    estimator._restart_runner = lambda run_one, starts: run_sharded(run_one, starts, group, schedule)
+    Every rank ends with the same fitted estimator (same kernel_, L_, alpha_).  pilot_rows: hand the runs out longest
+    first, lengths guessed by `pilot_order` (off by default)."""
+    t0 = time.perf_counter()
+    order = pilot_order(estimator, X, y, pilot_rows, group) if pilot_rows else None
+    estimator.pilot_order_, estimator.pilot_seconds_ = order, time.perf_counter() - t0
+
+    def runner(run_one, starts):
+        use = order if (order is not None and len(order) == len(starts)) else None
+        return run_sharded(run_one, starts, group, schedule, use)
+    estimator._restart_runner = runner
     try:
         return estimator.fit(X, y)
     finally:
