@@ -16,6 +16,7 @@ from unmanned_aerial_vehicles_b200.parallel import fit_sharded_restarts
 ap = argparse.ArgumentParser()
 ap.add_argument("--size", dest="n", type=int, default=20000)
 ap.add_argument("--restarts", type=int, default=9)
+ap.add_argument("--pilot-rows", type=int, default=0, help="hand the runs out longest first, lengths guessed by a pilot fit on this many rows (0: plain queue)")
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
 torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
@@ -35,7 +36,7 @@ t0 = time.perf_counter()
 with warnings.catch_warnings():
     warnings.simplefilter("ignore")
     if world > 1:
-        fit_sharded_restarts(g, X, Y)
+        fit_sharded_restarts(g, X, Y, pilot_rows=a.pilot_rows or None)
     else:
         g.fit(X, Y)
 torch.cuda.synchronize()
@@ -46,7 +47,8 @@ if world > 1:
 if rank == 0:
     out = {"what": "full_fit", "config": f"config2: N={a.n} D={D} T={T}, {a.restarts + 1} L-BFGS-B runs, random_state=0",
            "n_gpus": world, "fit_seconds": float(dt[0]), "lml_evaluations_all_ranks": int(ev[0]),
-           "lml": float(g.log_marginal_likelihood_value_), "kernel": str(g.kernel_)}
+           "lml": float(g.log_marginal_likelihood_value_), "kernel": str(g.kernel_),
+           "pilot_rows": a.pilot_rows, "pilot_order": getattr(g, "pilot_order_", None), "pilot_seconds": getattr(g, "pilot_seconds_", None)}
     print(json.dumps(out), flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
     open("gpurun_out/full_fit.jsonl", "a").write(json.dumps(out) + "\n")
